@@ -1,0 +1,253 @@
+"""ctypes front-end of the CPU oracle (oracle/m3s_oracle.c).
+
+TEST INFRASTRUCTURE ONLY -- the parity checker and the timed CPU baseline.  Only tests/,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this
+module; the product package (mast3r-slam_b200/) never does.
+
+Function signatures mirror the reference's operator API
+(/root/reference/src/mlx_mast3r_slam/backends/mpsgraph/kernels.py:107,262,325,396,463) so that
+parity tests read like calls into the reference.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libm3s_oracle.so")
+_lib = None
+
+
+def build(force: bool = False) -> str:
+    """Compile the C restatement (gcc, -ffp-contract=off).  Returns the .so path."""
+    src = os.path.join(_HERE, "m3s_oracle.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-s", "-C", _HERE, "CC=gcc"])
+    return _SO
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        _lib = C.CDLL(_SO)
+        _lib.m3s_oracle_num_threads.restype = C.c_int
+    return _lib
+
+
+def num_threads() -> int:
+    return int(lib().m3s_oracle_num_threads())
+
+
+def set_threads(n: int) -> None:
+    lib().m3s_oracle_set_threads(C.c_int(int(n)))
+
+
+def _p(a, ty):
+    return a.ctypes.data_as(C.POINTER(ty))
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _u8(a):
+    return np.ascontiguousarray(np.asarray(a).astype(bool)).view(np.uint8)
+
+
+def prep_for_iter_proj(X11, X21, idx_init=None):
+    """matching.py:134-175 (fp32).  X11, X21 [B,H,W,3] -> rays [B,H,W,9], pts [B,N,3], p_init [B,N,2]."""
+    X11, X21 = _f32(X11), _f32(X21)
+    b, h, w, _ = X11.shape
+    n = h * w
+    rays = np.empty((b, h, w, 9), np.float32)
+    pts = np.empty((b, n, 3), np.float32)
+    p0 = np.empty((b, n, 2), np.float32)
+    ii = None if idx_init is None else _i32(idx_init)
+    rc = lib().m3s_oracle_prep_iter_proj(
+        _p(X11, C.c_float), _p(X21, C.c_float), None if ii is None else _p(ii, C.c_int32),
+        _p(rays, C.c_float), _p(pts, C.c_float), _p(p0, C.c_float), b, h, w)
+    assert rc == 0
+    return rays, pts, p0
+
+
+def iter_proj(rays_with_grad, pts3d_norm, p_init, max_iter=10, lambda_init=1e-8,
+              convergence_thresh=1e-6, return_iters=False):
+    """kernels.py:151-254."""
+    rays, pts, p0 = _f32(rays_with_grad), _f32(pts3d_norm), _f32(p_init)
+    b, h, w, _ = rays.shape
+    n = pts.shape[1]
+    p = np.empty((b, n, 2), np.float32)
+    valid = np.empty((b, n), np.uint8)
+    it = C.c_int(0)
+    rc = lib().m3s_oracle_iter_proj(
+        _p(rays, C.c_float), _p(pts, C.c_float), _p(p0, C.c_float), _p(p, C.c_float),
+        _p(valid, C.c_uint8), b, h, w, n, int(max_iter), C.c_float(lambda_init),
+        C.c_float(convergence_thresh), C.byref(it))
+    assert rc == 0
+    if return_iters:
+        return p, valid.astype(bool), it.value
+    return p, valid.astype(bool)
+
+
+def refine_matches(D11, D21, p1, radius=3, dilation_max=0):
+    """kernels.py:496-537."""
+    D11, D21 = _f32(D11), _f32(D21)
+    p1 = np.ascontiguousarray(np.asarray(p1).astype(np.int32))  # int(p1[...]) truncates
+    b, h, w, d = D11.shape
+    n = p1.shape[1]
+    out = np.empty((b, n, 2), np.int32)
+    rc = lib().m3s_oracle_refine_matches(
+        _p(D11, C.c_float), _p(D21, C.c_float), _p(p1, C.c_int32), _p(out, C.c_int32),
+        b, h, w, d, n, int(radius), int(dilation_max))
+    assert rc == 0
+    return out
+
+
+def match_tail(X11, X21, p1_int, valid_proj, dist_thresh=0.1):
+    """matching.py:438-461 -> (idx [B,N] i32, valid [B,N,1] bool)."""
+    X11, X21 = _f32(X11), _f32(X21)
+    b, h, w, _ = X11.shape
+    n = h * w
+    p1 = _i32(p1_int)
+    vp = _u8(valid_proj)
+    idx = np.empty((b, n), np.int32)
+    valid = np.empty((b, n), np.uint8)
+    rc = lib().m3s_oracle_match_tail(
+        _p(X11, C.c_float), _p(X21, C.c_float), _p(p1, C.c_int32), _p(vp, C.c_uint8),
+        _p(idx, C.c_int32), _p(valid, C.c_uint8), b, h, w, C.c_float(dist_thresh))
+    assert rc == 0
+    return idx, valid.astype(bool)[:, :, None]
+
+
+def match_iterative_proj(X11, X21, D11, D21, idx_init=None, max_iter=10, lambda_init=1e-8,
+                         convergence_thresh=1e-6, radius=3, dilation_max=2, dist_thresh=0.1):
+    """matching.py:339-461 end to end on the CPU oracle."""
+    b, h, w, _ = np.asarray(X11).shape
+    rays, pts, p0 = prep_for_iter_proj(X11, X21, idx_init)
+    p, vproj = iter_proj(rays, pts, p0, max_iter, lambda_init, convergence_thresh)
+    p1 = p.astype(np.int32)
+    if radius > 0:
+        p1 = refine_matches(np.asarray(D11).reshape(b, h, w, -1),
+                            np.asarray(D21).reshape(b, h * w, -1), p1, radius, dilation_max)
+    return match_tail(X11, X21, p1, vproj, dist_thresh)
+
+
+def _gn(mode, Twc, Xs, Cs, Kmat, ii, jj, idx, valid, Q, img_size, pixel_border, z_eps, sigma_a,
+        sigma_b, C_thresh, Q_thresh, max_iter, delta_thresh, pin, debug=False):
+    Twc, Xs = _f32(Twc), _f32(Xs)
+    Cs, Q = np.asarray(Cs), np.asarray(Q)
+    valid = np.asarray(valid)
+    if Cs.ndim == 3:
+        Cs = Cs[..., 0]
+    if Q.ndim == 3:
+        Q = Q[..., 0]
+    if valid.ndim == 3:
+        valid = valid[..., 0]
+    Cs, Q, valid = _f32(Cs), _f32(Q), _u8(valid)
+    ii, jj, idx = _i32(ii), _i32(jj), _i32(idx)
+    nkf, n = Xs.shape[0], Xs.shape[1]
+    e = len(ii)
+    if Kmat is None:
+        k4 = np.zeros(4, np.float32)
+    else:
+        Kmat = np.asarray(Kmat)
+        k4 = (np.array([Kmat[0, 0], Kmat[1, 1], Kmat[0, 2], Kmat[1, 2]]) if Kmat.shape == (3, 3)
+              else Kmat.flatten()[:4]).astype(np.float32)
+    out = np.empty((nkf, 8), np.float32)
+    nu = len(np.unique(np.concatenate([ii, jj]))) if e else 0
+    dim = 7 * max(nu - pin, 0)
+    dx = np.zeros((max(max_iter, 1), max(dim, 1)), np.float64)
+    Hg = np.zeros(max(dim * dim + dim, 1), np.float64)
+    its = C.c_int(0)
+    f = lib().m3s_oracle_gauss_newton(
+        int(mode), _p(Twc, C.c_float), _p(Xs, C.c_float), _p(Cs, C.c_float), _p(k4, C.c_float),
+        _p(ii, C.c_int32), _p(jj, C.c_int32), _p(idx, C.c_int32), _p(valid, C.c_uint8),
+        _p(Q, C.c_float), nkf, C.c_long(n), e, int(img_size[0]), int(img_size[1]),
+        int(pixel_border), C.c_double(z_eps), C.c_double(sigma_a), C.c_double(sigma_b),
+        C.c_double(C_thresh), C.c_double(Q_thresh), int(max_iter), C.c_double(delta_thresh),
+        int(pin), _p(out, C.c_float), _p(dx, C.c_double), _p(Hg, C.c_double), C.byref(its))
+    assert f >= 0
+    if debug:
+        return out, dict(F=f, dx=dx[:, :dim], H=Hg[:dim * dim].reshape(dim, dim),
+                         g=Hg[dim * dim:dim * dim + dim], iters=its.value)
+    return out
+
+
+def gauss_newton_rays(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_ray=0.003,
+                      sigma_dist=10.0, C_thresh=0.0, Q_thresh=1.5, max_iter=10, delta_thresh=1e-4,
+                      pin=1, debug=False):
+    """gauss_newton.py:23-280 (sigma_dist is accepted and unused, as in the reference)."""
+    return _gn(0, Twc, Xs, Cs, None, ii, jj, idx_ii2jj, valid_match, Q, (0, 0), 0, 0.0, sigma_ray,
+               0.0, C_thresh, Q_thresh, max_iter, delta_thresh, pin, debug)
+
+
+def gauss_newton_points(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_point=0.01,
+                        C_thresh=0.0, Q_thresh=1.5, max_iter=10, delta_thresh=1e-4, pin=1,
+                        debug=False):
+    """gauss_newton_points.py:17-207."""
+    return _gn(1, Twc, Xs, Cs, None, ii, jj, idx_ii2jj, valid_match, Q, (0, 0), 0, 0.0,
+               sigma_point, 0.0, C_thresh, Q_thresh, max_iter, delta_thresh, pin, debug)
+
+
+def gauss_newton_calib(Twc, Xs, Cs, K, ii, jj, idx_ii2jj, valid_match, Q, img_size,
+                       pixel_border=0, z_eps=0.0, sigma_pixel=1.0, sigma_depth=0.1, C_thresh=0.0,
+                       Q_thresh=1.5, max_iter=10, delta_thresh=1e-4, pin=1, debug=False):
+    """gauss_newton_calib.py:17-274."""
+    return _gn(2, Twc, Xs, Cs, K, ii, jj, idx_ii2jj, valid_match, Q, img_size, pixel_border, z_eps,
+               sigma_pixel, sigma_depth, C_thresh, Q_thresh, max_iter, delta_thresh, pin, debug)
+
+
+# ---------------------------------------------------------------------------------------------
+# numpy restatements of the MLX-only host steps (cannot be imported from the reference: they need
+# `mlx`).  Used to cross-check the C versions above at small sizes.
+# ---------------------------------------------------------------------------------------------
+def prep_for_iter_proj_numpy(X11, X21, idx_init=None):
+    """matching.py:134-175 + image.py:9-34 restated with numpy fp32 ops."""
+    X11 = np.asarray(X11, np.float32)
+    X21 = np.asarray(X21, np.float32)
+    b, h, w, _ = X11.shape
+
+    def normalize(X):
+        sq = X * X
+        s = (sq[..., 0] + sq[..., 1]) + sq[..., 2]
+        return X / np.sqrt(s + np.float32(1e-10))[..., None]
+
+    rays = normalize(X11)
+    gx = np.zeros_like(rays)
+    gy = np.zeros_like(rays)
+    gx[:, :, 1:-1] = (rays[:, :, 2:] - rays[:, :, :-2]) / np.float32(2.0)
+    gy[:, 1:-1] = (rays[:, 2:] - rays[:, :-2]) / np.float32(2.0)
+    rwg = np.concatenate([rays, gx, gy], axis=-1)
+    pts = normalize(X21.reshape(b, -1, 3))
+    if idx_init is None:
+        idx_init = np.broadcast_to(np.arange(h * w)[None], (b, h * w))
+    idx_init = np.asarray(idx_init)
+    p0 = np.stack([idx_init % w, idx_init // w], axis=-1).astype(np.float32)
+    return rwg, pts, p0
+
+
+def match_tail_numpy(X11, X21, p1_int, valid_proj, dist_thresh=0.1):
+    """matching.py:438-461 restated with numpy."""
+    X11 = np.asarray(X11, np.float32)
+    X21 = np.asarray(X21, np.float32)
+    b, h, w, _ = X11.shape
+    p1_int = np.asarray(p1_int, np.int32)
+    y = np.clip(p1_int[..., 1], 0, h - 1)
+    x = np.clip(p1_int[..., 0], 0, w - 1)
+    lin = y * w + x
+    X11f = X11.reshape(b, h * w, 3)
+    samp = np.stack([X11f[bi, lin[bi]] for bi in range(b)])
+    d = (samp - X21.reshape(b, h * w, 3)) ** 2
+    dist = np.sqrt((d[..., 0] + d[..., 1]) + d[..., 2])
+    valid = np.asarray(valid_proj, bool) & (dist < np.float32(dist_thresh))
+    idx = p1_int[..., 0] + w * p1_int[..., 1]
+    return idx.astype(np.int32), valid[:, :, None]
