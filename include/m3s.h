@@ -1,0 +1,189 @@
+/*
+ * m3s.h -- C ABI of the B200-native (sm_100a) MASt3R-SLAM backend hot path:
+ *   iterative projective matching (iter_proj) -> descriptor refine_matches -> match tail, and
+ *   Sim3 Gauss-Newton (rays / points / calib): accumulate -> assemble -> damped solve -> retract.
+ *
+ * This is the drop-in boundary.  Every entry point replaces one function of the reference's
+ * operator layer (paths relative to /root/reference/src/mlx_mast3r_slam/), cited per function.
+ * The reference is Python: its "FFI" for this path is the numpy-in / numpy-out operator module
+ * backends/mpsgraph/kernels.py, which a maintainer would re-point at this library with the ctypes
+ * stub shown in INTEGRATION.md (our own copy of that stub is mast3r-slam_b200/_lib.py).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / numpy types.  Unless a parameter name ends in
+ *     `_host`, pointers are DEVICE pointers (cudaMalloc / torch CUDA tensors), densely packed,
+ *     row-major, with the layouts of the reference's numpy arrays.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  All work is
+ *     enqueued asynchronously on it; no entry point synchronises unless documented.
+ *   - return value: 0 = ok, <0 = error (M3S_ERR_*); m3s_last_error() returns a thread-local
+ *     message.  There is NO CPU fallback: without a CUDA device every compute entry point fails
+ *     with M3S_ERR_CUDA.
+ *   - inputs are never modified; outputs are caller-allocated.
+ */
+#ifndef M3S_H_
+#define M3S_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define M3S_OK 0
+#define M3S_ERR_INVALID (-1)   /* bad argument (null pointer, non-positive size, ...) */
+#define M3S_ERR_CUDA (-2)      /* CUDA runtime error or no device */
+#define M3S_ERR_WORKSPACE (-3) /* workspace too small */
+#define M3S_ERR_UNSUPPORTED (-4)
+
+#define M3S_GN_RAYS 0   /* gauss_newton_rays   (backends/mpsgraph/gauss_newton.py:23)        */
+#define M3S_GN_POINTS 1 /* gauss_newton_points (backends/mpsgraph/gauss_newton_points.py:17) */
+#define M3S_GN_CALIB 2  /* gauss_newton_calib  (backends/mpsgraph/gauss_newton_calib.py:17)  */
+
+typedef void* m3s_stream_t;
+
+/* ---- library ------------------------------------------------------------------------------ */
+int m3s_version(void);              /* 100 * major + minor */
+const char* m3s_last_error(void);   /* thread-local, never NULL */
+int m3s_device_count(void);         /* CUDA devices visible to this process (0 if none) */
+int m3s_sm_count(int device);       /* multiprocessor count of `device` (<0 on error) */
+
+/* ---- matching ------------------------------------------------------------------------------ */
+
+/* Replaces prep_for_iter_proj (matching.py:134-175) incl. normalize_rays (:121-131),
+ * img_gradient (image.py:9-34) and lin_to_pixel (matching.py:106-118).
+ *   X11, X21 [B,H,W,3] f32; idx_init [B,H*W] i32 or NULL (identity)
+ *   -> rays_out [B,H,W,9] f32 = (ray, d/dx, d/dy), pts_out [B,H*W,3], p_init_out [B,H*W,2]. */
+int m3s_prep_iter_proj(const float* X11, const float* X21, const int32_t* idx_init,
+                       float* rays_out, float* pts_out, float* p_init_out, int B, int H, int W,
+                       m3s_stream_t stream);
+
+/* Scratch bytes m3s_iter_proj needs (per-iteration max-step slots for the global early exit). */
+size_t m3s_iter_proj_workspace_bytes(int max_iter);
+
+/* Replaces iter_proj (backends/mpsgraph/kernels.py:107-148), numpy semantics of
+ * _iter_proj_numpy (:151-254): <=max_iter Levenberg-Marquardt steps per point on the bilinearly
+ * sampled 9-channel ray image, fp64 blend weights, GLOBAL early exit when the largest step of an
+ * iteration is < convergence_thresh (resolved on the device: no host synchronisation).
+ *   rays [B,H,W,9], pts [B,N,3], p_init [B,N,2]  ->  p_out [B,N,2] f32 (clamped), valid_out [B,N] u8
+ * Bit-exact against the reference's numpy path for finite inputs.  NaN positions yield valid=0. */
+int m3s_iter_proj(const float* rays, const float* pts, const float* p_init, float* p_out,
+                  uint8_t* valid_out, int B, int H, int W, int N, int max_iter, float lambda_init,
+                  float convergence_thresh, void* workspace, size_t workspace_bytes,
+                  m3s_stream_t stream);
+
+/* Replaces refine_matches (backends/mpsgraph/kernels.py:463-493), numpy semantics of
+ * _refine_matches_numpy (:496-537): argmax over the (2*radius+1)^2 window (step 1; dilation_max
+ * is accepted and, exactly as in the reference's numpy path, has no effect) of <D21[n], D11[y,x]>,
+ * scan dy outer / dx inner, strict '>', out-of-image candidates skipped.
+ *   D11 [B,H,W,D] f32, D21 [B,N,D] f32, p1 [B,N,2] i32 -> p1_out [B,N,2] i32 */
+int m3s_refine_matches(const float* D11, const float* D21, const int32_t* p1, int32_t* p1_out,
+                       int B, int H, int W, int D, int N, int radius, int dilation_max,
+                       m3s_stream_t stream);
+
+/* Same, taking the float positions iter_proj produced; the `p1.astype(int32)` truncation of
+ * matching.py:410 is fused into the load. */
+int m3s_refine_matches_f32(const float* D11, const float* D21, const float* p1, int32_t* p1_out,
+                           int B, int H, int W, int D, int N, int radius, int dilation_max,
+                           m3s_stream_t stream);
+
+/* Replaces the tail of match_iterative_proj (matching.py:438-461):
+ *   gather X11 at clip(p1), valid = valid_proj & (||X11[p1] - X21|| < dist_thresh),
+ *   idx = p1.x + W * p1.y.     X11, X21 [B,H,W,3]; p1 [B,H*W,2] i32; valid_proj [B,H*W] u8
+ *   -> idx_out [B,H*W] i32, valid_out [B,H*W] u8 (the caller views it as [B,H*W,1]). */
+int m3s_match_tail(const float* X11, const float* X21, const int32_t* p1,
+                   const uint8_t* valid_proj, int32_t* idx_out, uint8_t* valid_out, int B, int H,
+                   int W, float dist_thresh, m3s_stream_t stream);
+
+/* Whole match_iterative_proj (matching.py:339-461) on device-resident inputs:
+ * prep -> iter_proj -> trunc -> refine_matches -> tail, intermediates in `workspace`.
+ *   X11, X21 [B,H,W,3]; D11, D21 [B,H,W,D]; idx_init [B,H*W] i32 or NULL
+ *   -> idx_out [B,H*W] i32, valid_out [B,H*W] u8.   radius <= 0 skips the refinement. */
+size_t m3s_match_workspace_bytes(int B, int H, int W, int max_iter);
+int m3s_match_iterative_proj(const float* X11, const float* X21, const float* D11,
+                             const float* D21, const int32_t* idx_init, int32_t* idx_out,
+                             uint8_t* valid_out, int B, int H, int W, int D, int max_iter,
+                             float lambda_init, float convergence_thresh, int radius,
+                             int dilation_max, float dist_thresh, void* workspace,
+                             size_t workspace_bytes, m3s_stream_t stream);
+
+/* ---- Gauss-Newton -------------------------------------------------------------------------- */
+
+/* Scalars of gauss_newton_{rays,points,calib} (backends/mpsgraph/kernels.py:262-279, 325-346,
+ * 396-412).  sigma_a = sigma_ray | sigma_point | sigma_pixel; sigma_b = sigma_depth (calib). */
+typedef struct m3s_gn_params {
+    int32_t mode;         /* M3S_GN_* */
+    int32_t max_iter;
+    int32_t pin;
+    int32_t pixel_border; /* calib */
+    int32_t img_w, img_h; /* calib: img_size = (width, height) */
+    double sigma_a, sigma_b;
+    double C_thresh, Q_thresh;
+    double delta_thresh;
+    double z_eps;         /* calib */
+    float K4[4];          /* calib: fx, fy, cx, cy (the reference passes K as fp32) */
+} m3s_gn_params;
+
+/* Per-graph plan: the free-keyframe numbering of gauss_newton.py:70-78 (sorted unique(ii U jj),
+ * first `pin` fixed), the deterministic H/g assembly lists (gauss_newton.py:222-251) and all
+ * device workspaces (fp64 poses, per-edge blocks, dense H, g, dx).  Topology arrays are HOST
+ * pointers.  `device` = CUDA device ordinal.  Returns NULL on error (see m3s_last_error). */
+typedef struct m3s_gn_plan m3s_gn_plan;
+m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii_host, const int32_t* jj_host, int E, int num_kf,
+                                int64_t N, int pin, int device);
+void m3s_gn_plan_destroy(m3s_gn_plan* plan);
+int m3s_gn_plan_num_free(const m3s_gn_plan* plan);      /* F; 0 => solver is a no-op (early out) */
+int m3s_gn_plan_dim(const m3s_gn_plan* plan);           /* 7 F */
+int m3s_gn_plan_ld(const m3s_gn_plan* plan);            /* row stride of H: dim rounded up to 32 */
+/* device pointer + element count of the packed per-edge blocks [E][M3S_GN_EDGE_STRIDE] f64 that
+ * m3s_gn_accumulate writes and m3s_gn_solve_update reads: the buffer a multi-GPU caller
+ * all-reduces (sum) between the two when edges are sharded across ranks. */
+#define M3S_GN_EDGE_STRIDE 36
+double* m3s_gn_plan_edge_blocks(m3s_gn_plan* plan, int64_t* count_out);
+double* m3s_gn_plan_H(m3s_gn_plan* plan);   /* [dim rows, ld] f64 (device): H + 1e-6 I after
+                                               m3s_gn_assemble; overwritten by its Cholesky
+                                               factor (lower) in m3s_gn_solve_update */
+double* m3s_gn_plan_g(m3s_gn_plan* plan);   /* [dim] */
+double* m3s_gn_plan_dx(m3s_gn_plan* plan);  /* [dim] last solved step */
+
+/* Load poses Twc [num_kf,8] f32 (tx,ty,tz,qx,qy,qz,qw,s) into the plan's fp64 state
+ * (gauss_newton.py:92-94) and reset the iteration status. */
+int m3s_gn_set_poses(m3s_gn_plan* plan, const float* Twc, m3s_stream_t stream);
+/* Write the fp64 state back as f32 (gauss_newton.py:279). */
+int m3s_gn_get_poses(m3s_gn_plan* plan, float* Twc_out, m3s_stream_t stream);
+
+/* One residual/Jacobian/reduction pass over directed edges [edge_begin, edge_end)
+ * (gauss_newton.py:106-220; Metal gn_jacobian_kernel gauss_newton.metal:66-252):
+ * per edge the symmetric 7x7 block and 7-vector in the pose-free basis, reduced warp -> block ->
+ * fixed-order chunk sum (no atomics); slots of edges outside the range are zero-filled so a
+ * sum all-reduce over ranks reproduces the single-GPU buffer bit for bit.
+ *   Xs [K,N,3] f32, Cs [K,N] f32, idx [E,N] i32, valid [E,N] u8, Q [E,N] f32. */
+int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* params, const float* Xs,
+                      const float* Cs, const int32_t* idx, const uint8_t* valid, const float* Q,
+                      int edge_begin, int edge_end, m3s_stream_t stream);
+
+/* Assemble only: dense H (+ 1e-6 I, gauss_newton.py:254) and g from the per-edge blocks through
+ * fixed-order lists (gauss_newton.py:222-251).  m3s_gn_solve_update calls it itself; exposed for
+ * inspection and tests. */
+int m3s_gn_assemble(m3s_gn_plan* plan, m3s_stream_t stream);
+
+/* Assemble dense H, g from the per-edge blocks (gauss_newton.py:222-251), H += 1e-6 I, solve
+ * H dx = -g by Cholesky (:254-260), test ||dx|| < delta_thresh BEFORE applying (:263-265),
+ * retract the free poses T <- exp(dx) o T (sim3_ops.py:229-251).  Entirely on the device. */
+int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* params, m3s_stream_t stream);
+
+/* status_host[0] = iterations applied, [1] = 1 if stopped by the delta test, [2] = 1 if the solve
+ * failed (non-finite / not positive definite), [3] = iterations attempted.  Synchronises. */
+int m3s_gn_status(m3s_gn_plan* plan, int32_t* status_host, double* last_dx_norm_host,
+                  m3s_stream_t stream);
+
+/* Whole solver: gauss_newton_rays / _points / _calib of backends/mpsgraph/kernels.py:262,396,325.
+ *   Twc [K,8] f32 device -> Twc_out [K,8] f32 device.  No host synchronisation. */
+int m3s_gauss_newton(m3s_gn_plan* plan, const m3s_gn_params* params, const float* Twc,
+                     const float* Xs, const float* Cs, const int32_t* idx, const uint8_t* valid,
+                     const float* Q, float* Twc_out, m3s_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* M3S_H_ */

@@ -1,0 +1,999 @@
+// Sim3 Gauss-Newton on the device: accumulate -> per-edge finalise -> assemble -> blocked fp64
+// Cholesky -> back-substitution + convergence test + retraction.  No host synchronisation and no
+// atomics anywhere; every reduction has a fixed order (bitwise reproducible, also across ranks).
+//
+// Reference: backends/mpsgraph/gauss_newton.py:23-280 (rays), gauss_newton_points.py:17-207,
+// gauss_newton_calib.py:17-274, sim3_ops.py (relative pose, Huber, exp/retract).
+//
+// Algebra used: in all three modes Ji = -Jj, and
+//     Jj = J' * G,   J' = P * [ s_i^-1 I | M | X' ],   G = blockdiag(R_i, R_i, 1),
+// with X' = T_ij Xj, M = -[X']x as the reference writes it (gauss_newton.py:172-182), R_i = R(q_i),
+// and P = I (rays / points) or the 3x3 projection Jacobian (calib).  G is constant per edge, so the
+// per-point work accumulates S = sum J'^T W J' and v = sum J'^T W err in the pose-free basis (29
+// sums for rays/points thanks to the sparsity of J', 35 for calib); the edge block is
+// A = G^T S G, b = G^T v, and  H_ii += A, H_jj += A, H_ij -= A, H_ji -= A, g_i -= b, g_j += b.
+#include <algorithm>
+#include <map>
+#include <new>
+#include <utility>
+#include <vector>
+
+#include "m3s_common.cuh"
+
+namespace m3s {
+
+constexpr int kAccThreads = 256;
+constexpr int kNB = 32;            // Cholesky panel width
+constexpr int kEdgeStride = M3S_GN_EDGE_STRIDE;
+constexpr double kHuber = 1.345;   // sim3_ops.py:295
+constexpr double kReg = 1e-6;      // gauss_newton.py:254
+
+struct Status {
+    int applied;    // iterations whose update was applied
+    int stopped;    // ||dx|| < delta_thresh hit
+    int failed;     // factorisation failed / non-finite
+    int attempted;  // iterations attempted
+    int chol_fail;  // scratch flag of the running factorisation
+    int pad[3];
+    double last_norm;
+};
+
+struct EdgeMeta {
+    int ix, jx;   // keyframe rows of Xs / poses
+    int il, jl;   // local free index or -1
+    int active;   // contributes to H, g
+    int pad[3];
+};
+
+struct KernelParams {
+    int mode;
+    float sig_inv_f;              // f32(1/sigma_ray | 1/sigma_point)
+    float c_th, q_th;             // f32 thresholds (numpy compares f32 arrays with weak scalars)
+    float fx, fy, cx, cy;         // calib
+    double z_eps, sig_px_inv, sig_z_inv;
+    double u_lo, u_hi, v_lo, v_hi;  // border <= u < W - border
+};
+
+// ------------------------------------------------------------------------------------------------
+// small fp64 Sim3 helpers
+// ------------------------------------------------------------------------------------------------
+__host__ __device__ inline void quat_mul(const double* a, const double* b, double* o) {
+    const double x1 = a[0], y1 = a[1], z1 = a[2], w1 = a[3];
+    const double x2 = b[0], y2 = b[1], z2 = b[2], w2 = b[3];
+    o[0] = w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2;
+    o[1] = w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2;
+    o[2] = w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2;
+    o[3] = w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2;
+}
+
+// linear map of sim3_ops.quat_rotate: R = I + 2w[q]x + 2[q]x^2 (valid for non-unit q as well)
+__host__ __device__ inline void quat_to_mat(const double* q, double* R) {
+    const double x = q[0], y = q[1], z = q[2], w = q[3];
+    R[0] = 1.0 - 2.0 * (y * y + z * z); R[1] = 2.0 * (x * y - z * w); R[2] = 2.0 * (x * z + y * w);
+    R[3] = 2.0 * (x * y + z * w); R[4] = 1.0 - 2.0 * (x * x + z * z); R[5] = 2.0 * (y * z - x * w);
+    R[6] = 2.0 * (x * z - y * w); R[7] = 2.0 * (y * z + x * w); R[8] = 1.0 - 2.0 * (x * x + y * y);
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: accumulate.  grid = nchunks * E blocks; block (e, chunk) streams points
+// [chunk*chunk_pts, ...) of directed edge e.
+//   per point reads: idx 4 + valid 1 + Q 4 (edge streams), Xj 12 + Cj 4 (coalesced), Xi 12 + Ci 4
+//   (gather through idx) = 41 B; compulsory traffic 9 B/(edge,pt) + 16 B/(kf,pt).
+// Per-thread fp64 accumulators -> warp shuffle tree -> shared across warps -> one partial per
+// block.  No atomics.
+// ------------------------------------------------------------------------------------------------
+template <int MODE> struct AccCount { static constexpr int value = 29; };
+template <> struct AccCount<M3S_GN_CALIB> { static constexpr int value = 35; };
+
+struct EdgeConst {
+    double sR[9];   // s_ij * R(q_ij)
+    double t[3];    // t_ij
+    double s_inv;   // 1 / s_i
+};
+
+template <int MODE>
+__device__ __forceinline__ void accumulate_point(const KernelParams& P, const EdgeConst& ec,
+                                                 float xjx, float xjy, float xjz, float xix,
+                                                 float xiy, float xiz, float qc, double* acc) {
+    const double Xj0 = xjx, Xj1 = xjy, Xj2 = xjz;
+    const double x = ec.sR[0] * Xj0 + ec.sR[1] * Xj1 + ec.sR[2] * Xj2 + ec.t[0];
+    const double y = ec.sR[3] * Xj0 + ec.sR[4] * Xj1 + ec.sR[5] * Xj2 + ec.t[1];
+    const double z = ec.sR[6] * Xj0 + ec.sR[7] * Xj1 + ec.sR[8] * Xj2 + ec.t[2];
+    if (MODE == M3S_GN_CALIB) {
+        // gauss_newton_calib.py:125-221.  Observed side (Xi, fp32 K) is evaluated in fp32 exactly as
+        // numpy does (f32 arrays times np.float32 scalars), predicted side in fp64.
+        if (!(z > P.z_eps) || !((double)xiz > P.z_eps)) return;
+        const double zinv = 1.0 / z;
+        const float zinv_i = __fdiv_rn(1.0f, xiz);
+        const double pju = (double)P.fx * x * zinv + (double)P.cx;
+        const double pjv = (double)P.fy * y * zinv + (double)P.cy;
+        if (!(pju >= P.u_lo && pju < P.u_hi && pjv >= P.v_lo && pjv < P.v_hi)) return;
+        const float piu = __fadd_rn(__fmul_rn(__fmul_rn(P.fx, xix), zinv_i), P.cx);
+        const float piv = __fadd_rn(__fmul_rn(__fmul_rn(P.fy, xiy), zinv_i), P.cy);
+        const double e0 = (pju - (double)piu) * P.sig_px_inv;
+        const double e1 = (pjv - (double)piv) * P.sig_px_inv;
+        const double e2 = (log(z) - (double)logf(xiz)) * P.sig_z_inv;
+        const float sw = __fsqrt_rn(qc);
+        const double sqrt_w = sw, w2 = (double)__fmul_rn(sw, sw);
+        const double zinv2 = zinv * zinv;
+        const double pa = (double)P.fx * zinv * P.sig_px_inv;
+        const double pb = -(double)P.fx * x * zinv2 * P.sig_px_inv;
+        const double pc = (double)P.fy * zinv * P.sig_px_inv;
+        const double pd = -(double)P.fy * y * zinv2 * P.sig_px_inv;
+        const double pe = zinv * P.sig_z_inv;
+        const double si = ec.s_inv;
+        // rows of J' = P [ si I | M | X' ],  M = [[0,z,-y],[-z,0,x],[y,-x,0]]
+        const double J[3][7] = {
+            {pa * si, 0.0, pb * si, pb * y, pa * z - pb * x, -pa * y, pa * x + pb * z},
+            {0.0, pc * si, pd * si, -pc * z + pd * y, -pd * x, pc * x, pc * y + pd * z},
+            {0.0, 0.0, pe * si, pe * y, -pe * x, 0.0, pe * z}};
+        const double err[3] = {e0, e1, e2};
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const double ra = fabs(sqrt_w * err[c]);
+            const double w = (ra < kHuber) ? w2 : (kHuber / ra) * w2;
+            int k = 0;
+#pragma unroll
+            for (int a = 0; a < 7; ++a) {
+                const double wj = w * J[c][a];
+#pragma unroll
+                for (int b = a; b < 7; ++b) acc[k++] += wj * J[c][b];
+                acc[28 + a] += wj * err[c];
+            }
+        }
+    } else {
+        const double e0 = x - (double)xix, e1 = y - (double)xiy, e2 = z - (double)xiz;
+        float sw = __fmul_rn(P.sig_inv_f, __fsqrt_rn(qc));  // gauss_newton.py:147 (f32)
+        if (MODE == M3S_GN_POINTS) {
+            // gauss_newton_points.py:115-119: f32 norm + 1e-6, f32 reciprocal
+            float ss = __fmul_rn(xix, xix);
+            ss = __fadd_rn(ss, __fmul_rn(xiy, xiy));
+            ss = __fadd_rn(ss, __fmul_rn(xiz, xiz));
+            const float dist = __fadd_rn(__fsqrt_rn(ss), 1e-6f);
+            sw = __fmul_rn(sw, __fdiv_rn(1.0f, dist));
+        }
+        const double sqrt_w = sw, w2 = (double)__fmul_rn(sw, sw);
+        const double r0 = fabs(sqrt_w * e0), r1 = fabs(sqrt_w * e1), r2 = fabs(sqrt_w * e2);
+        const double w0 = (r0 < kHuber) ? w2 : (kHuber / r0) * w2;
+        const double w1 = (r1 < kHuber) ? w2 : (kHuber / r1) * w2;
+        const double w2c = (r2 < kHuber) ? w2 : (kHuber / r2) * w2;
+        const double w0y = w0 * y, w0z = w0 * z, w1x = w1 * x, w1z = w1 * z, w2x = w2c * x,
+                     w2y = w2c * y;
+        const double w0x = w0 * x, w1y = w1 * y, w2z = w2c * z;
+        acc[0] += w0; acc[1] += w1; acc[2] += w2c;
+        acc[3] += w0z; acc[4] += w0y; acc[5] += w1z; acc[6] += w1x; acc[7] += w2y; acc[8] += w2x;
+        acc[9] += w0x; acc[10] += w1y; acc[11] += w2z;
+        acc[12] += w1z * z + w2y * y;
+        acc[13] += w0z * z + w2x * x;
+        acc[14] += w0y * y + w1x * x;
+        acc[15] += w2x * y;
+        acc[16] += w1x * z;
+        acc[17] += w0y * z;
+        acc[18] += (w2y - w1y) * z;   // yz (w2 - w1)
+        acc[19] += (w0x - w2x) * z;   // xz (w0 - w2)
+        acc[20] += (w1x - w0x) * y;   // xy (w1 - w0)
+        acc[21] += w0x * x + w1y * y + w2z * z;
+        const double u0 = w0 * e0, u1 = w1 * e1, u2 = w2c * e2;
+        acc[22] += u0; acc[23] += u1; acc[24] += u2;
+        acc[25] += y * u2 - z * u1;
+        acc[26] += z * u0 - x * u2;
+        acc[27] += x * u1 - y * u0;
+        acc[28] += x * u0 + y * u1 + z * u2;
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kAccThreads)
+gn_accum_kernel(const Status* __restrict__ status, KernelParams P, const double* __restrict__ poses,
+                const EdgeMeta* __restrict__ meta, const float* __restrict__ Xs,
+                const float* __restrict__ Cs, const int32_t* __restrict__ idx,
+                const uint8_t* __restrict__ valid, const float* __restrict__ Q, long long N,
+                int edge_begin, int nchunks, long long chunk_pts, double* __restrict__ partials) {
+    if (status->stopped | status->failed) return;
+    constexpr int NA = AccCount<MODE>::value;
+    const int e = edge_begin + blockIdx.x / nchunks;
+    const int chunk = blockIdx.x % nchunks;
+    const EdgeMeta em = meta[e];
+    double* out = partials + ((size_t)e * nchunks + chunk) * kEdgeStride;
+    if (!em.active) return;  // slot is zeroed by the finalise kernel
+
+    __shared__ EdgeConst ec_s;
+    __shared__ double red[kAccThreads / 32][NA];
+    if (threadIdx.x == 0) {
+        // sim3_relative (sim3_ops.py:96-126)
+        const double* Ti = poses + 8 * em.ix;
+        const double* Tj = poses + 8 * em.jx;
+        const double si_inv = 1.0 / Ti[7];
+        const double sij = si_inv * Tj[7];
+        const double qi_inv[4] = {-Ti[3], -Ti[4], -Ti[5], Ti[6]};
+        double qij[4], R[9], Ri[9];
+        quat_mul(qi_inv, Tj + 3, qij);
+        quat_to_mat(qij, R);
+        quat_to_mat(qi_inv, Ri);
+        const double d0 = Tj[0] - Ti[0], d1 = Tj[1] - Ti[1], d2 = Tj[2] - Ti[2];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) ec_s.sR[k] = R[k] * sij;
+        ec_s.t[0] = (Ri[0] * d0 + Ri[1] * d1 + Ri[2] * d2) * si_inv;
+        ec_s.t[1] = (Ri[3] * d0 + Ri[4] * d1 + Ri[5] * d2) * si_inv;
+        ec_s.t[2] = (Ri[6] * d0 + Ri[7] * d1 + Ri[8] * d2) * si_inv;
+        ec_s.s_inv = si_inv;
+    }
+    __syncthreads();
+    const EdgeConst ec = ec_s;
+
+    double acc[NA];
+#pragma unroll
+    for (int k = 0; k < NA; ++k) acc[k] = 0.0;
+
+    const float* __restrict__ Xi = Xs + (size_t)em.ix * N * 3;
+    const float* __restrict__ Ci = Cs + (size_t)em.ix * N;
+    const float* __restrict__ Xj = Xs + (size_t)em.jx * N * 3;
+    const float* __restrict__ Cj = Cs + (size_t)em.jx * N;
+    const int32_t* __restrict__ ide = idx + (size_t)e * N;
+    const uint8_t* __restrict__ ve = valid + (size_t)e * N;
+    const float* __restrict__ Qe = Q + (size_t)e * N;
+
+    const long long n0 = (long long)chunk * chunk_pts;
+    const long long n1 = min(N, n0 + chunk_pts);
+    for (long long n = n0 + threadIdx.x; n < n1; n += kAccThreads) {
+        if (!__ldg(ve + n)) continue;
+        const float qc = __ldg(Qe + n);
+        long long m = __ldg(ide + n);
+        if (m < 0) m += N;  // numpy negative indexing (gauss_newton.py:125)
+        if (m < 0 || m >= N) continue;
+        if (!(qc > P.q_th) || !(__ldg(Cj + n) > P.c_th) || !(__ldg(Ci + m) > P.c_th)) continue;
+        accumulate_point<MODE>(P, ec, __ldg(Xj + 3 * n), __ldg(Xj + 3 * n + 1), __ldg(Xj + 3 * n + 2),
+                               __ldg(Xi + 3 * m), __ldg(Xi + 3 * m + 1), __ldg(Xi + 3 * m + 2), qc,
+                               acc);
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NA; ++k) {
+        const double v = warp_sum(acc[k]);
+        if (lane == 0) red[warp][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < NA) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < kAccThreads / 32; ++w) s += red[w][threadIdx.x];
+        out[threadIdx.x] = s;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Per-edge finalise: fixed-order sum over chunks, unpack to S (7x7) and v (7), transform by
+// G = blockdiag(R_i, R_i, 1), write 28 upper + 7 (+1 spare) doubles per edge.  Edges outside
+// [edge_begin, edge_end) and inactive edges get zeros (all-reduce friendly).  One 64-thread block
+// per edge.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int tri_index(int r, int c) {  // r <= c, 7x7 upper
+    return r * 7 - (r * (r - 1)) / 2 + (c - r);
+}
+
+__global__ void __launch_bounds__(64)
+gn_edge_finalize_kernel(const Status* __restrict__ status, int mode,
+                        const double* __restrict__ poses, const EdgeMeta* __restrict__ meta,
+                        const double* __restrict__ partials, int nchunks, int edge_begin,
+                        int edge_end, double* __restrict__ edge_blocks) {
+    if (status->stopped | status->failed) return;
+    const int e = blockIdx.x;
+    const int tid = threadIdx.x;
+    double* out = edge_blocks + (size_t)e * kEdgeStride;
+    const EdgeMeta em = meta[e];
+    if (e < edge_begin || e >= edge_end || !em.active) {
+        if (tid < kEdgeStride) out[tid] = 0.0;
+        return;
+    }
+    __shared__ double acc[kEdgeStride];
+    __shared__ double S[7][7], v[7], G[7][7], T[7][7];
+    const int NA = (mode == M3S_GN_CALIB) ? 35 : 29;
+    if (tid < NA) {
+        const double* p = partials + (size_t)e * nchunks * kEdgeStride + tid;
+        double s = 0.0;
+        for (int c = 0; c < nchunks; ++c) s += p[(size_t)c * kEdgeStride];
+        acc[tid] = s;
+    }
+    if (tid < 49) G[tid / 7][tid % 7] = 0.0;
+    __syncthreads();
+    if (tid == 0) {
+        const double* Ti = poses + 8 * em.ix;
+        // R_i: Jj[c, :3] = s_i^-1 * R(q_i^-1) e_c = s_i^-1 * (row c of R(q_i)) etc.
+        double Ri[9];
+        quat_to_mat(Ti + 3, Ri);
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) { G[r][c] = Ri[r * 3 + c]; G[3 + r][3 + c] = Ri[r * 3 + c]; }
+        G[6][6] = 1.0;
+        if (mode == M3S_GN_CALIB) {
+            int k = 0;
+            for (int a = 0; a < 7; ++a)
+                for (int b = a; b < 7; ++b) { S[a][b] = acc[k]; S[b][a] = acc[k]; ++k; }
+            for (int a = 0; a < 7; ++a) v[a] = acc[28 + a];
+        } else {
+            const double si = 1.0 / Ti[7];
+            const double* a = acc;
+            for (int r = 0; r < 7; ++r)
+                for (int c = 0; c < 7; ++c) S[r][c] = 0.0;
+            S[0][0] = si * si * a[0]; S[1][1] = si * si * a[1]; S[2][2] = si * si * a[2];
+            S[0][4] = si * a[3];  S[0][5] = -si * a[4];
+            S[1][3] = -si * a[5]; S[1][5] = si * a[6];
+            S[2][3] = si * a[7];  S[2][4] = -si * a[8];
+            S[0][6] = si * a[9]; S[1][6] = si * a[10]; S[2][6] = si * a[11];
+            S[3][3] = a[12]; S[4][4] = a[13]; S[5][5] = a[14];
+            S[3][4] = -a[15]; S[3][5] = -a[16]; S[4][5] = -a[17];
+            S[3][6] = a[18]; S[4][6] = a[19]; S[5][6] = a[20];
+            S[6][6] = a[21];
+            for (int r = 0; r < 7; ++r)
+                for (int c = r + 1; c < 7; ++c) S[c][r] = S[r][c];
+            v[0] = si * a[22]; v[1] = si * a[23]; v[2] = si * a[24];
+            v[3] = a[25]; v[4] = a[26]; v[5] = a[27]; v[6] = a[28];
+        }
+    }
+    __syncthreads();
+    if (tid < 49) {  // T = S G
+        const int r = tid / 7, c = tid % 7;
+        double s = 0.0;
+        for (int k = 0; k < 7; ++k) s += S[r][k] * G[k][c];
+        T[r][c] = s;
+    }
+    __syncthreads();
+    if (tid < 49) {  // A = G^T T (upper part stored)
+        const int r = tid / 7, c = tid % 7;
+        if (r <= c) {
+            double s = 0.0;
+            for (int k = 0; k < 7; ++k) s += G[k][r] * T[k][c];
+            out[tri_index(r, c)] = s;
+        }
+    } else if (tid < 56) {  // b = G^T v
+        const int r = tid - 49;
+        double s = 0.0;
+        for (int k = 0; k < 7; ++k) s += G[k][r] * v[k];
+        out[28 + r] = s;
+    } else if (tid == 56) {
+        out[35] = 0.0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Assemble dense H (lower + upper), g (as the extra row "-g" of the augmented matrix) from the
+// per-edge blocks through CSR lists built on the host: deterministic, no atomics.
+// Matrix storage: row-major [np + 1][np], np = dim rounded up to a multiple of 32; padded diagonal
+// entries are 1 (so the padded factor is blockdiag(L, I)); row np holds -g (the right-hand side):
+// factorising the augmented matrix performs the forward substitution on the fly.
+// ------------------------------------------------------------------------------------------------
+struct BlockRef {
+    int row, col;     // local free ids; row == col for diagonal blocks; row > col otherwise
+    int begin, end;   // range in the edge list
+};
+
+__global__ void __launch_bounds__(64)
+gn_assemble_kernel(const Status* __restrict__ status, const BlockRef* __restrict__ blocks,
+                   const int* __restrict__ list_edge, const int* __restrict__ list_sign,
+                   const double* __restrict__ edge_blocks, double* __restrict__ Hm, int np, int dim,
+                   double* __restrict__ g_out) {
+    if (status->stopped | status->failed) return;
+    const BlockRef br = blocks[blockIdx.x];
+    const int tid = threadIdx.x;
+    if (tid < 49) {
+        const int r = tid / 7, c = tid % 7;
+        const int k = (r <= c) ? tri_index(r, c) : tri_index(c, r);
+        double s = 0.0;
+        for (int l = br.begin; l < br.end; ++l) s += edge_blocks[(size_t)list_edge[l] * kEdgeStride + k];
+        if (br.row == br.col) {
+            if (r == c) s += kReg;
+            Hm[(size_t)(br.row * 7 + r) * np + br.col * 7 + c] = s;
+        } else {
+            s = -s;
+            Hm[(size_t)(br.row * 7 + r) * np + br.col * 7 + c] = s;
+            Hm[(size_t)(br.col * 7 + c) * np + br.row * 7 + r] = s;
+        }
+    } else if (tid < 56 && br.row == br.col) {
+        const int r = tid - 49;
+        double s = 0.0;
+        for (int l = br.begin; l < br.end; ++l)
+            s += (double)list_sign[l] * edge_blocks[(size_t)list_edge[l] * kEdgeStride + 28 + r];
+        g_out[br.row * 7 + r] = s;
+        Hm[(size_t)np * np + br.row * 7 + r] = -s;  // rhs row of the augmented matrix
+    }
+    (void)dim;
+}
+
+// identity on the padded diagonal (dim .. np-1); rhs row padding is zero from the memset
+__global__ void gn_pad_diag_kernel(const Status* __restrict__ status, double* __restrict__ Hm,
+                                   int np, int dim) {
+    if (status->stopped | status->failed) return;
+    const int k = dim + blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < np) Hm[(size_t)k * np + k] = 1.0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Blocked right-looking Cholesky of the augmented matrix (lower triangle, in place), panel = 32.
+//   step k: (a) every CTA factorises the 32x32 diagonal block redundantly in shared memory (no
+//               extra launch / grid sync), CTA 0 stores it to Ldiag[k]; each thread then solves
+//               one row of the panel below:  L21 = A21 L11^-T  (right-looking inside the row,
+//               row in registers);
+//           (b) trailing update A22 -= L21 L21^T on 64x64 tiles of the lower triangle (+ rhs row).
+// ------------------------------------------------------------------------------------------------
+constexpr int kTrsmRows = 128;
+
+__global__ void __launch_bounds__(kTrsmRows)
+chol_panel_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* __restrict__ Ldiag,
+                  int np, int k0) {
+    if (status->stopped | status->failed | status->chol_fail) return;
+    __shared__ double D[kNB][kNB + 1];
+    __shared__ double dinv[kNB];
+    __shared__ int bad;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < kNB * kNB; i += blockDim.x) {
+        const int r = i / kNB, c = i % kNB;
+        D[r][c] = (c <= r) ? Hm[(size_t)(k0 + r) * np + k0 + c] : 0.0;
+    }
+    if (tid == 0) bad = 0;
+    __syncthreads();
+    if (tid < 32) {
+        // warp-level unblocked Cholesky: lane = row
+        const int r = tid;
+        for (int j = 0; j < kNB; ++j) {
+            double djj = D[j][j];
+            const bool ok = (djj > 0.0) && (djj == djj) && (djj < 1e300);
+            if (!ok) { if (r == 0) bad = 1; djj = 1.0; }
+            const double ljj = sqrt(djj);
+            const double inv = 1.0 / ljj;
+            __syncwarp();
+            if (r == j) { D[j][j] = ljj; dinv[j] = inv; }
+            double lrj = 0.0;
+            if (r > j) { lrj = D[r][j] * inv; D[r][j] = lrj; }
+            __syncwarp();
+            // trailing update of row r: D[r][c] -= L[r][j] * L[c][j] for j < c <= r
+            if (r > j)
+                for (int c = j + 1; c <= r; ++c) D[r][c] -= lrj * D[c][j];
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+    if (bad) {
+        if (blockIdx.x == 0 && tid == 0) status->chol_fail = 1;
+        return;
+    }
+    if (blockIdx.x == 0) {
+        double* Ld = Ldiag + (size_t)(k0 / kNB) * kNB * kNB;
+        for (int i = tid; i < kNB * kNB; i += blockDim.x) Ld[i] = D[i / kNB][i % kNB];
+    }
+    // rows below the diagonal block, including the rhs row np
+    const int row = k0 + kNB + blockIdx.x * kTrsmRows + tid;
+    if (row > np) return;
+    double* a = Hm + (size_t)row * np + k0;
+    double x[kNB];
+#pragma unroll
+    for (int c = 0; c < kNB; ++c) x[c] = a[c];
+#pragma unroll
+    for (int j = 0; j < kNB; ++j) {
+        const double xj = x[j] * dinv[j];
+        x[j] = xj;
+#pragma unroll
+        for (int c = j + 1; c < kNB; ++c) x[c] -= xj * D[c][j];
+    }
+#pragma unroll
+    for (int c = 0; c < kNB; ++c) a[c] = x[c];
+}
+
+constexpr int kSyrkTile = 64;
+
+__global__ void __launch_bounds__(256)
+chol_syrk_kernel(const Status* __restrict__ status, double* __restrict__ Hm, int np, int k0) {
+    if (status->stopped | status->failed | status->chol_fail) return;
+    const int tr = blockIdx.y, tc = blockIdx.x;
+    if (tc > tr) return;
+    const int base = k0 + kNB;
+    const int r0 = base + tr * kSyrkTile, c0 = base + tc * kSyrkTile;
+    __shared__ double A[kSyrkTile][kNB + 1];
+    __shared__ double B[kSyrkTile][kNB + 1];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < kSyrkTile * kNB; i += 256) {
+        const int r = i / kNB, c = i % kNB;
+        const int gr = r0 + r, gc = c0 + r;
+        A[r][c] = (gr <= np) ? Hm[(size_t)gr * np + k0 + c] : 0.0;
+        B[r][c] = (gc < np) ? Hm[(size_t)gc * np + k0 + c] : 0.0;
+    }
+    __syncthreads();
+    const int ty = tid / 16, tx = tid % 16;  // 16 x 16 threads, 4 x 4 outputs each (strided by 16)
+    double acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+#pragma unroll 8
+    for (int k = 0; k < kNB; ++k) {
+        double a[4], b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { a[i] = A[ty + 16 * i][k]; b[i] = B[tx + 16 * i][k]; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] += a[i] * b[j];
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int gr = r0 + ty + 16 * i;
+        if (gr > np) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int gc = c0 + tx + 16 * j;
+            if (gc < np && gc <= gr) Hm[(size_t)gr * np + gc] -= acc[i][j];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Back-substitution L^T dx = y (y = rhs row of the factorised augmented matrix), ||dx|| test
+// (gauss_newton.py:263-265: stop BEFORE applying) and Sim3 retraction (sim3_ops.py:129-251) in one
+// single-CTA kernel.
+// ------------------------------------------------------------------------------------------------
+__device__ void sim3_retract_dev(const double* xi, double* T) {
+    const double EPS = 1e-6;
+    const double* tau = xi;
+    const double* om = xi + 3;
+    const double sigma = xi[6];
+    const double th2 = om[0] * om[0] + om[1] * om[1] + om[2] * om[2];
+    const double th = sqrt(th2 + EPS);  // biased on purpose, as the reference
+    const bool small_t = th2 < EPS, small_s = fabs(sigma) < EPS;
+    const double imag = small_t ? 0.5 - th2 / 48.0 : sin(0.5 * th) / th;
+    const double real = small_t ? 1.0 - th2 / 8.0 : cos(0.5 * th);
+    const double dq[4] = {imag * om[0], imag * om[1], imag * om[2], real};
+    const double s = exp(sigma);
+    const double C = small_s ? 1.0 : (s - 1.0) / sigma;
+    double A, Bc;
+    if (small_s) {
+        A = small_t ? 0.5 : (1.0 - cos(th)) / th2;
+        Bc = small_t ? 1.0 / 6.0 : (th - sin(th)) / (th2 * th);
+    } else if (small_t) {
+        A = ((sigma - 1.0) * s + 1.0) / (sigma * sigma);
+        Bc = (s * 0.5 * sigma * sigma + s - 1.0 - sigma * s) / (sigma * sigma * sigma);
+    } else {
+        A = (s * sin(th) * sigma + (1.0 - s * cos(th)) * th) / (th * (th2 + sigma * sigma));
+        Bc = (C - ((s * cos(th) - 1.0) * sigma + s * sin(th) * th) / (th2 + sigma * sigma)) / th2;
+    }
+    const double c1[3] = {om[1] * tau[2] - om[2] * tau[1], om[2] * tau[0] - om[0] * tau[2],
+                          om[0] * tau[1] - om[1] * tau[0]};
+    const double c2[3] = {om[1] * c1[2] - om[2] * c1[1], om[2] * c1[0] - om[0] * c1[2],
+                          om[0] * c1[1] - om[1] * c1[0]};
+    double qn[4], R[9];
+    quat_mul(dq, T + 3, qn);
+    quat_to_mat(dq, R);
+    const double t0 = T[0], t1 = T[1], t2 = T[2];
+    T[0] = (R[0] * t0 + R[1] * t1 + R[2] * t2) * s + (C * tau[0] + A * c1[0] + Bc * c2[0]);
+    T[1] = (R[3] * t0 + R[4] * t1 + R[5] * t2) * s + (C * tau[1] + A * c1[1] + Bc * c2[1]);
+    T[2] = (R[6] * t0 + R[7] * t1 + R[8] * t2) * s + (C * tau[2] + A * c1[2] + Bc * c2[2]);
+    T[3] = qn[0]; T[4] = qn[1]; T[5] = qn[2]; T[6] = qn[3];
+    T[7] = s * T[7];
+}
+
+constexpr int kSolveThreads = 1024;
+
+__global__ void __launch_bounds__(kSolveThreads)
+gn_backsolve_update_kernel(Status* __restrict__ status, const double* __restrict__ Hm,
+                           const double* __restrict__ Ldiag, int np, int dim, int num_free,
+                           const int* __restrict__ free_kf, double delta_thresh,
+                           double* __restrict__ dx_out, double* __restrict__ poses) {
+    if (status->stopped | status->failed) return;
+    extern __shared__ double ysh[];  // [np]
+    __shared__ double red[kSolveThreads / 32];
+    __shared__ int decision;  // 0 apply, 1 stop, 2 fail
+    const int tid = threadIdx.x;
+    if (status->chol_fail) {
+        if (tid == 0) { status->failed = 1; status->attempted += 1; status->chol_fail = 0; }
+        return;
+    }
+    for (int i = tid; i < np; i += blockDim.x) ysh[i] = Hm[(size_t)np * np + i];
+    __syncthreads();
+    const int nblk = np / kNB;
+    for (int b = nblk - 1; b >= 0; --b) {
+        if (tid < 32) {
+            // solve L_bb^T x = y_b : lane i owns y_i; columns of L_bb^T are rows of L_bb
+            const double* Ld = Ldiag + (size_t)b * kNB * kNB;
+            double yi = ysh[b * kNB + tid];
+            for (int j = kNB - 1; j >= 0; --j) {
+                double xj = 0.0;
+                if (tid == j) xj = yi / Ld[j * kNB + j];
+                xj = __shfl_sync(0xffffffffu, xj, j);
+                if (tid == j) yi = xj;
+                else if (tid < j) yi -= Ld[j * kNB + tid] * xj;
+            }
+            ysh[b * kNB + tid] = yi;
+        }
+        __syncthreads();
+        // y_c -= sum_{r in block b} L[r][c] x_r  for all columns c left of the block
+        const int ncol = b * kNB;
+        for (int c = tid; c < ncol; c += blockDim.x) {
+            double s = ysh[c];
+            const double* Lr = Hm + (size_t)(b * kNB) * np + c;
+#pragma unroll 8
+            for (int r = 0; r < kNB; ++r) s -= Lr[(size_t)r * np] * ysh[b * kNB + r];
+            ysh[c] = s;
+        }
+        __syncthreads();
+    }
+    // ||dx||_2 and finiteness
+    double part = 0.0;
+    int nonfinite = 0;
+    for (int i = tid; i < dim; i += blockDim.x) {
+        const double v = ysh[i];
+        dx_out[i] = v;
+        part += v * v;
+        if (!(fabs(v) <= 1.7e308)) nonfinite = 1;
+    }
+    part = warp_sum(part);
+    nonfinite = __any_sync(0xffffffffu, nonfinite);
+    if ((tid & 31) == 0) red[tid >> 5] = nonfinite ? __longlong_as_double(0x7ff8000000000000LL) : part;
+    __syncthreads();
+    if (tid == 0) {
+        double s = 0.0;
+        for (int w = 0; w < kSolveThreads / 32; ++w) s += red[w];
+        const double nrm = sqrt(s);
+        status->last_norm = nrm;
+        status->attempted += 1;
+        int d;
+        if (!(nrm == nrm)) d = 2;                 // non-finite step: treat as failed solve
+        else if (nrm < delta_thresh) d = 1;       // converged: do not apply
+        else d = 0;
+        if (d == 1) status->stopped = 1;
+        if (d == 2) status->failed = 1;
+        if (d == 0) status->applied += 1;
+        decision = d;
+    }
+    __syncthreads();
+    if (decision != 0) return;
+    for (int f = tid; f < num_free; f += blockDim.x) sim3_retract_dev(ysh + 7 * f, poses + 8 * free_kf[f]);
+}
+
+__global__ void gn_poses_f32_to_f64(const float* __restrict__ in, double* __restrict__ out, int n,
+                                    Status* status) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (double)in[i];
+    if (i == 0 && status) {
+        status->applied = 0; status->stopped = 0; status->failed = 0; status->attempted = 0;
+        status->chol_fail = 0; status->last_norm = 0.0;
+    }
+}
+
+__global__ void gn_poses_f64_to_f32(const double* __restrict__ in, float* __restrict__ out, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (float)in[i];
+}
+
+}  // namespace m3s
+
+using namespace m3s;
+
+// ------------------------------------------------------------------------------------------------
+// plan
+// ------------------------------------------------------------------------------------------------
+struct m3s_gn_plan {
+    int device = 0;
+    int E = 0, num_kf = 0, pin = 0;
+    long long N = 0;
+    int F = 0, dim = 0, np = 0;
+    int nchunks = 1;
+    long long chunk_pts = 0;
+    int nblocks_H = 0;
+    // device buffers
+    double* poses = nullptr;        // [num_kf, 8]
+    EdgeMeta* meta = nullptr;       // [E]
+    double* partials = nullptr;     // [E, nchunks, 36]
+    double* edge_blocks = nullptr;  // [E, 36]
+    BlockRef* blocks = nullptr;
+    int* list_edge = nullptr;
+    int* list_sign = nullptr;
+    int* free_kf = nullptr;         // [F]
+    double* Hm = nullptr;           // [np + 1, np]
+    double* Ldiag = nullptr;        // [np / 32, 32, 32]
+    double* g = nullptr;            // [dim]
+    double* dx = nullptr;           // [dim]
+    Status* status = nullptr;
+};
+
+static void plan_free(m3s_gn_plan* p) {
+    if (!p) return;
+    cudaFree(p->poses); cudaFree(p->meta); cudaFree(p->partials); cudaFree(p->edge_blocks);
+    cudaFree(p->blocks); cudaFree(p->list_edge); cudaFree(p->list_sign); cudaFree(p->free_kf);
+    cudaFree(p->Hm); cudaFree(p->Ldiag); cudaFree(p->g); cudaFree(p->dx); cudaFree(p->status);
+    delete p;
+}
+
+template <typename T>
+static bool dev_alloc_copy(T** dst, const std::vector<T>& src) {
+    const size_t bytes = std::max<size_t>(src.size(), 1) * sizeof(T);
+    if (cudaMalloc(reinterpret_cast<void**>(dst), bytes) != cudaSuccess) return false;
+    if (!src.empty() && cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess)
+        return false;
+    return true;
+}
+
+M3S_API m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii, const int32_t* jj, int E, int num_kf,
+                                        int64_t N, int pin, int device) {
+    if (E < 0 || num_kf < 0 || N < 0 || pin < 0 || (E > 0 && (!ii || !jj))) {
+        set_error("gn_plan_create: bad argument");
+        return nullptr;
+    }
+    for (int e = 0; e < E; ++e) {
+        if (ii[e] < 0 || ii[e] >= num_kf || jj[e] < 0 || jj[e] >= num_kf) {
+            set_error("gn_plan_create: edge %d references keyframe outside [0, %d)", e, num_kf);
+            return nullptr;
+        }
+    }
+    int cur_dev = -1;
+    cudaGetDevice(&cur_dev);
+    if (cur_dev != device && cudaSetDevice(device) != cudaSuccess) {
+        cuda_fail(cudaGetLastError(), "cudaSetDevice");
+        return nullptr;
+    }
+    struct Restore { int d, want; ~Restore() { if (d >= 0 && d != want) cudaSetDevice(d); } } restore{cur_dev, device};
+    m3s_gn_plan* p = new (std::nothrow) m3s_gn_plan();
+    if (!p) { set_error("gn_plan_create: out of memory"); return nullptr; }
+    p->device = device; p->E = E; p->num_kf = num_kf; p->pin = pin; p->N = N;
+
+    // free-keyframe numbering: gauss_newton.py:66-81
+    std::vector<int> uniq;
+    if (E > 0 && num_kf > pin) {
+        uniq.assign(ii, ii + E);
+        uniq.insert(uniq.end(), jj, jj + E);
+        std::sort(uniq.begin(), uniq.end());
+        uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+    }
+    const int nu = (int)uniq.size();
+    p->F = (nu > pin) ? nu - pin : 0;
+    p->dim = 7 * p->F;
+    p->np = ((p->dim + kNB - 1) / kNB) * kNB;
+    std::vector<int> local(std::max(num_kf, 1), -1);
+    std::vector<int> free_kf;
+    for (int k = pin; k < nu; ++k) { local[uniq[k]] = k - pin; free_kf.push_back(uniq[k]); }
+
+    std::vector<EdgeMeta> meta(E);
+    int n_active = 0;
+    for (int e = 0; e < E; ++e) {
+        EdgeMeta m{};
+        m.ix = ii[e]; m.jx = jj[e];
+        m.il = p->F ? local[m.ix] : -1;
+        m.jl = p->F ? local[m.jx] : -1;
+        // both ends fixed: skipped by the reference (gauss_newton.py:113); self edge: its four
+        // contributions cancel exactly (H_ii + H_jj - H_ij - H_ji = 0, g_i + g_j = 0)
+        m.active = (m.il >= 0 || m.jl >= 0) && (m.ix != m.jx);
+        n_active += m.active;
+        meta[e] = m;
+    }
+    // assembly lists
+    std::vector<BlockRef> blocks;
+    std::vector<int> list_edge, list_sign;
+    if (p->F > 0) {
+        std::vector<std::vector<std::pair<int, int>>> diag(p->F);
+        std::map<std::pair<int, int>, std::vector<int>> off;
+        for (int e = 0; e < E; ++e) {
+            const EdgeMeta& m = meta[e];
+            if (!m.active) continue;
+            if (m.il >= 0) diag[m.il].push_back({e, -1});  // g_i -= b
+            if (m.jl >= 0) diag[m.jl].push_back({e, +1});  // g_j += b
+            if (m.il >= 0 && m.jl >= 0) {
+                const int hi = std::max(m.il, m.jl), lo = std::min(m.il, m.jl);
+                off[{hi, lo}].push_back(e);
+            }
+        }
+        for (int f = 0; f < p->F; ++f) {
+            BlockRef b{f, f, (int)list_edge.size(), 0};
+            for (auto& pr : diag[f]) { list_edge.push_back(pr.first); list_sign.push_back(pr.second); }
+            b.end = (int)list_edge.size();
+            blocks.push_back(b);
+        }
+        for (auto& kv : off) {
+            BlockRef b{kv.first.first, kv.first.second, (int)list_edge.size(), 0};
+            for (int e : kv.second) { list_edge.push_back(e); list_sign.push_back(0); }
+            b.end = (int)list_edge.size();
+            blocks.push_back(b);
+        }
+    }
+    p->nblocks_H = (int)blocks.size();
+
+    // chunking of the point dimension: aim for >= ~6 CTAs per SM in flight, 1024..8192 pts/CTA
+    {
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        const long long target_blocks = 6LL * sms;
+        long long nch = (n_active > 0) ? (target_blocks + n_active - 1) / n_active : 1;
+        const long long max_ch = std::max<long long>(1, (N + 1023) / 1024);
+        const long long min_ch = std::max<long long>(1, (N + 8191) / 8192);
+        nch = std::min(std::max(nch, min_ch), max_ch);
+        long long cp = (N + nch - 1) / std::max<long long>(nch, 1);
+        cp = std::max<long long>(((cp + kAccThreads - 1) / kAccThreads) * kAccThreads, kAccThreads);
+        p->chunk_pts = cp;
+        p->nchunks = (int)std::max<long long>(1, (N + cp - 1) / cp);
+    }
+
+    bool ok = true;
+    ok = ok && cudaMalloc((void**)&p->poses, sizeof(double) * 8 * std::max(num_kf, 1)) == cudaSuccess;
+    ok = ok && dev_alloc_copy(&p->meta, meta);
+    ok = ok && cudaMalloc((void**)&p->partials, sizeof(double) * kEdgeStride * (size_t)std::max(E, 1) * p->nchunks) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&p->edge_blocks, sizeof(double) * kEdgeStride * (size_t)std::max(E, 1)) == cudaSuccess;
+    ok = ok && dev_alloc_copy(&p->blocks, blocks);
+    ok = ok && dev_alloc_copy(&p->list_edge, list_edge);
+    ok = ok && dev_alloc_copy(&p->list_sign, list_sign);
+    ok = ok && dev_alloc_copy(&p->free_kf, free_kf);
+    const size_t hm = (size_t)(p->np + 1) * std::max(p->np, 1);
+    ok = ok && cudaMalloc((void**)&p->Hm, sizeof(double) * hm) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&p->Ldiag, sizeof(double) * kNB * std::max(p->np, kNB)) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&p->g, sizeof(double) * std::max(p->dim, 1)) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&p->dx, sizeof(double) * std::max(p->dim, 1)) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&p->status, sizeof(Status)) == cudaSuccess;
+    if (ok) {
+        ok = cudaMemset(p->status, 0, sizeof(Status)) == cudaSuccess &&
+             cudaMemset(p->edge_blocks, 0, sizeof(double) * kEdgeStride * (size_t)std::max(E, 1)) == cudaSuccess &&
+             cudaMemset(p->dx, 0, sizeof(double) * std::max(p->dim, 1)) == cudaSuccess &&
+             cudaMemset(p->g, 0, sizeof(double) * std::max(p->dim, 1)) == cudaSuccess;
+    }
+    if (!ok) {
+        cuda_fail(cudaGetLastError(), "gn_plan_create allocation");
+        plan_free(p);
+        return nullptr;
+    }
+    return p;
+}
+
+M3S_API void m3s_gn_plan_destroy(m3s_gn_plan* plan) { plan_free(plan); }
+M3S_API int m3s_gn_plan_num_free(const m3s_gn_plan* plan) { return plan ? plan->F : 0; }
+M3S_API int m3s_gn_plan_dim(const m3s_gn_plan* plan) { return plan ? plan->dim : 0; }
+M3S_API int m3s_gn_plan_ld(const m3s_gn_plan* plan) { return plan ? plan->np : 0; }
+M3S_API double* m3s_gn_plan_edge_blocks(m3s_gn_plan* plan, int64_t* count_out) {
+    if (!plan) return nullptr;
+    if (count_out) *count_out = (int64_t)plan->E * kEdgeStride;
+    return plan->edge_blocks;
+}
+M3S_API double* m3s_gn_plan_H(m3s_gn_plan* plan) { return plan ? plan->Hm : nullptr; }
+M3S_API double* m3s_gn_plan_g(m3s_gn_plan* plan) { return plan ? plan->g : nullptr; }
+M3S_API double* m3s_gn_plan_dx(m3s_gn_plan* plan) { return plan ? plan->dx : nullptr; }
+
+M3S_API int m3s_gn_set_poses(m3s_gn_plan* plan, const float* Twc, m3s_stream_t stream) {
+    M3S_REQUIRE(plan && Twc, "gn_set_poses: null pointer");
+    const int n = 8 * plan->num_kf;
+    if (n == 0) return M3S_OK;
+    gn_poses_f32_to_f64<<<(n + 255) / 256, 256, 0, as_stream(stream)>>>(Twc, plan->poses, n, plan->status);
+    return launch_ok("gn_poses_f32_to_f64");
+}
+
+M3S_API int m3s_gn_get_poses(m3s_gn_plan* plan, float* Twc_out, m3s_stream_t stream) {
+    M3S_REQUIRE(plan && Twc_out, "gn_get_poses: null pointer");
+    const int n = 8 * plan->num_kf;
+    if (n == 0) return M3S_OK;
+    gn_poses_f64_to_f32<<<(n + 255) / 256, 256, 0, as_stream(stream)>>>(plan->poses, Twc_out, n);
+    return launch_ok("gn_poses_f64_to_f32");
+}
+
+static KernelParams make_kernel_params(const m3s_gn_params* gp) {
+    KernelParams P{};
+    P.mode = gp->mode;
+    P.c_th = (float)gp->C_thresh;
+    P.q_th = (float)gp->Q_thresh;
+    if (gp->mode == M3S_GN_CALIB) {
+        P.fx = gp->K4[0]; P.fy = gp->K4[1]; P.cx = gp->K4[2]; P.cy = gp->K4[3];
+        P.z_eps = gp->z_eps;
+        P.sig_px_inv = 1.0 / gp->sigma_a;
+        P.sig_z_inv = 1.0 / gp->sigma_b;
+        P.u_lo = gp->pixel_border; P.u_hi = gp->img_w - gp->pixel_border;
+        P.v_lo = gp->pixel_border; P.v_hi = gp->img_h - gp->pixel_border;
+    } else {
+        P.sig_inv_f = (float)(1.0 / gp->sigma_a);
+    }
+    return P;
+}
+
+M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const float* Xs,
+                              const float* Cs, const int32_t* idx, const uint8_t* valid,
+                              const float* Q, int edge_begin, int edge_end, m3s_stream_t stream) {
+    M3S_REQUIRE(plan && gp, "gn_accumulate: null pointer");
+    M3S_REQUIRE(gp->mode >= 0 && gp->mode <= 2, "gn_accumulate: bad mode");
+    M3S_REQUIRE(edge_begin >= 0 && edge_end <= plan->E && edge_begin <= edge_end, "gn_accumulate: bad edge range");
+    if (plan->F == 0 || plan->E == 0) return M3S_OK;
+    M3S_REQUIRE(Xs && Cs && idx && valid && Q, "gn_accumulate: null pointer");
+    cudaStream_t st = as_stream(stream);
+    const KernelParams P = make_kernel_params(gp);
+    const int ne = edge_end - edge_begin;
+    if (ne > 0 && plan->N > 0) {
+        const unsigned grid = (unsigned)((long long)ne * plan->nchunks);
+#define M3S_ACC(MODE)                                                                           \
+    gn_accum_kernel<MODE><<<grid, kAccThreads, 0, st>>>(plan->status, P, plan->poses, plan->meta, \
+                                                        Xs, Cs, idx, valid, Q, plan->N,          \
+                                                        edge_begin, plan->nchunks,               \
+                                                        plan->chunk_pts, plan->partials)
+        if (gp->mode == M3S_GN_RAYS) M3S_ACC(M3S_GN_RAYS);
+        else if (gp->mode == M3S_GN_POINTS) M3S_ACC(M3S_GN_POINTS);
+        else M3S_ACC(M3S_GN_CALIB);
+#undef M3S_ACC
+        if (int rc = launch_ok("gn_accum_kernel")) return rc;
+    }
+    gn_edge_finalize_kernel<<<plan->E, 64, 0, st>>>(plan->status, gp->mode, plan->poses, plan->meta,
+                                                    plan->partials, (plan->N > 0) ? plan->nchunks : 0,
+                                                    edge_begin, edge_end, plan->edge_blocks);
+    return launch_ok("gn_edge_finalize_kernel");
+}
+
+M3S_API int m3s_gn_assemble(m3s_gn_plan* plan, m3s_stream_t stream) {
+    M3S_REQUIRE(plan, "gn_assemble: null plan");
+    if (plan->F == 0) return M3S_OK;
+    cudaStream_t st = as_stream(stream);
+    // NOTE: the memset is unconditional (cheap); kernels after a stop are no-ops and H is not
+    // consumed any more.
+    M3S_CUDA(cudaMemsetAsync(plan->Hm, 0, sizeof(double) * (size_t)(plan->np + 1) * plan->np, st));
+    gn_assemble_kernel<<<plan->nblocks_H, 64, 0, st>>>(plan->status, plan->blocks, plan->list_edge,
+                                                       plan->list_sign, plan->edge_blocks, plan->Hm,
+                                                       plan->np, plan->dim, plan->g);
+    if (int rc = launch_ok("gn_assemble_kernel")) return rc;
+    if (plan->np > plan->dim) {
+        gn_pad_diag_kernel<<<1, 32, 0, st>>>(plan->status, plan->Hm, plan->np, plan->dim);
+        if (int rc = launch_ok("gn_pad_diag_kernel")) return rc;
+    }
+    return M3S_OK;
+}
+
+M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_stream_t stream) {
+    M3S_REQUIRE(plan && gp, "gn_solve_update: null pointer");
+    if (plan->F == 0) return M3S_OK;
+    cudaStream_t st = as_stream(stream);
+    if (int rc = m3s_gn_assemble(plan, stream)) return rc;
+    const int np = plan->np;
+    for (int k0 = 0; k0 < np; k0 += kNB) {
+        const int rows_below = np + 1 - (k0 + kNB);  // incl. rhs row
+        const int grid = std::max(1, (rows_below + kTrsmRows - 1) / kTrsmRows);
+        chol_panel_kernel<<<grid, kTrsmRows, 0, st>>>(plan->status, plan->Hm, plan->Ldiag, np, k0);
+        if (int rc = launch_ok("chol_panel_kernel")) return rc;
+        const int trailing = np - (k0 + kNB);
+        if (rows_below > 0 && trailing >= 0) {
+            const int tr = (rows_below + kSyrkTile - 1) / kSyrkTile;
+            const int tc = std::max(1, (trailing + kSyrkTile - 1) / kSyrkTile);
+            if (trailing > 0) {
+                chol_syrk_kernel<<<dim3(tc, tr), 256, 0, st>>>(plan->status, plan->Hm, np, k0);
+                if (int rc = launch_ok("chol_syrk_kernel")) return rc;
+            }
+        }
+    }
+    const size_t sh = sizeof(double) * np;
+    if (sh > 48 * 1024) {
+        M3S_CUDA(cudaFuncSetAttribute(gn_backsolve_update_kernel,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+    }
+    gn_backsolve_update_kernel<<<1, kSolveThreads, sh, st>>>(plan->status, plan->Hm, plan->Ldiag, np,
+                                                            plan->dim, plan->F, plan->free_kf,
+                                                            gp->delta_thresh, plan->dx, plan->poses);
+    return launch_ok("gn_backsolve_update_kernel");
+}
+
+M3S_API int m3s_gn_status(m3s_gn_plan* plan, int32_t* status_host, double* last_dx_norm_host,
+                          m3s_stream_t stream) {
+    M3S_REQUIRE(plan, "gn_status: null plan");
+    Status s;
+    M3S_CUDA(cudaMemcpyAsync(&s, plan->status, sizeof(Status), cudaMemcpyDeviceToHost, as_stream(stream)));
+    M3S_CUDA(cudaStreamSynchronize(as_stream(stream)));
+    if (status_host) {
+        status_host[0] = s.applied; status_host[1] = s.stopped; status_host[2] = s.failed;
+        status_host[3] = s.attempted;
+    }
+    if (last_dx_norm_host) *last_dx_norm_host = s.last_norm;
+    return M3S_OK;
+}
+
+M3S_API int m3s_gauss_newton(m3s_gn_plan* plan, const m3s_gn_params* gp, const float* Twc,
+                             const float* Xs, const float* Cs, const int32_t* idx,
+                             const uint8_t* valid, const float* Q, float* Twc_out,
+                             m3s_stream_t stream) {
+    M3S_REQUIRE(plan && gp && Twc && Twc_out, "gauss_newton: null pointer");
+    if (int rc = m3s_gn_set_poses(plan, Twc, stream)) return rc;
+    if (plan->F > 0) {
+        for (int it = 0; it < gp->max_iter; ++it) {
+            if (int rc = m3s_gn_accumulate(plan, gp, Xs, Cs, idx, valid, Q, 0, plan->E, stream)) return rc;
+            if (int rc = m3s_gn_solve_update(plan, gp, stream)) return rc;
+        }
+    }
+    return m3s_gn_get_poses(plan, Twc_out, stream);
+}

@@ -1,0 +1,42 @@
+// Shared host/device helpers for the m3s-b200 kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "m3s.h"
+
+#define M3S_API extern "C" __attribute__((visibility("default")))
+
+namespace m3s {
+
+// thread-local error message behind m3s_last_error()
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+
+#define M3S_CUDA(call)                                              \
+    do {                                                            \
+        cudaError_t e__ = (call);                                   \
+        if (e__ != cudaSuccess) return ::m3s::cuda_fail(e__, #call); \
+    } while (0)
+
+#define M3S_REQUIRE(cond, msg)              \
+    do {                                    \
+        if (!(cond)) {                      \
+            ::m3s::set_error("%s", msg);    \
+            return M3S_ERR_INVALID;         \
+        }                                   \
+    } while (0)
+
+inline int launch_ok(const char* name) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, name);
+    return M3S_OK;
+}
+
+// number of SMs of the current device (cached per device)
+int sm_count_current();
+
+static inline cudaStream_t as_stream(m3s_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+
+}  // namespace m3s

@@ -1,0 +1,40 @@
+"""L2 matching host: drop-in for the hot-path entry points of the reference's ``matching.py``.
+
+``match`` (matching.py:12-38), ``match_iterative_proj`` (:339-461) and ``prep_for_iter_proj``
+(:134-175) keep the reference's names, argument order, tensor layouts and return values
+(idx [B,H*W] int32, valid [B,H*W,1] bool).  The reference's tensors are MLX arrays; here they are
+numpy arrays or torch CUDA tensors, and every arithmetic step runs in the sm_100a kernels
+(one C-ABI call enqueues prep -> iter_proj -> refine -> tail; nothing is copied back in between,
+unlike matching.py:374-377, 418-431).
+
+``match_simple`` (matching.py:41-90, the reference's *default* route) is a nearest-descriptor
+shortcut outside the north-star path and is not provided: ``match`` raises if the configuration
+asks for it, instead of silently doing something else.
+"""
+from __future__ import annotations
+
+from . import kernels
+from .config import get_config
+
+prep_for_iter_proj = kernels.prep_for_iter_proj
+
+
+def match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init=None):
+    """matching.py:339-461.  X11, X21 [B,H,W,3]; D11, D21 [B,H,W,D]; idx_init [B,H*W] or None."""
+    cfg = get_config()["matching"]
+    radius = cfg.get("refine_radius", 3)
+    use_refine = cfg.get("use_refine", True) and radius > 0
+    return kernels.match_iterative_proj_device(
+        X11, X21, D11, D21, idx_1_to_2_init, cfg["max_iter"], cfg["lambda_init"],
+        cfg["convergence_thresh"], radius if use_refine else 0, cfg.get("refine_dilation", 2),
+        cfg["dist_thresh"])
+
+
+def match(X11, X21, D11, D21, idx_1_to_2_init=None):
+    """matching.py:12-38: the config switch in front of match_iterative_proj."""
+    if get_config().get("matching", {}).get("use_simple", True):
+        raise NotImplementedError(
+            "matching.use_simple=True selects the reference's match_simple shortcut, which is "
+            "outside the accelerated path; set matching.use_simple=False (set_config) to use "
+            "match_iterative_proj")
+    return match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init)

@@ -1,0 +1,218 @@
+"""GPU parity tests for the Gauss-Newton stages (pytest -m gpu), through the C ABI.
+
+Bar (BASELINE.json north_star): pose/scale updates within 1e-5 relative of the reference's fp64
+numpy path.  Comparisons: golden vectors produced by the reference itself, the CPU oracle on seeded
+graphs (incl. H, g and dx of the first iteration in fp64), and a 200-keyframe graph."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+REL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def K():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from mast3r_slam_b200 import kernels
+    assert kernels.is_available(), "CUDA extension not loaded"
+    return kernels
+
+
+@pytest.fixture(scope="module")
+def synth():
+    from mast3r_slam_b200 import synth as s
+    return s
+
+
+def upd_err(out, ref, Twc):
+    """max |out - ref| relative to the size of the update the reference made (1e-5 bar), with one
+    float32 ulp of slack for the final cast (gauss_newton.py:279)."""
+    out, ref, Twc = (np.asarray(x, np.float64) for x in (out, ref, Twc))
+    upd = np.abs(ref - Twc).max()
+    slack = 1.2e-7 * np.abs(ref).max()
+    return max(np.abs(out - ref).max() - slack, 0.0) / max(upd, 1e-30)
+
+
+def gargs(g):
+    return [g[k] for k in ("Twc", "Xs", "Cs", "ii", "jj", "idx", "valid", "Q")]
+
+
+@pytest.mark.parametrize("it", [1, 2, 6])
+def test_gn_golden_graph(K, golden, it):
+    g = golden("gn_graph")
+    a = gargs(g)
+    assert upd_err(K.gauss_newton_rays(*a, max_iter=it), g[f"rays_it{it}"], g["Twc"]) <= REL
+    assert upd_err(K.gauss_newton_points(*a, max_iter=it), g[f"points_it{it}"], g["Twc"]) <= REL
+    out = K.gauss_newton_calib(g["Twc"], g["Xs"], g["Cs"], g["K3"], g["ii"], g["jj"], g["idx"],
+                               g["valid"], g["Q"], tuple(int(v) for v in g["img_size"]),
+                               pixel_border=1, z_eps=0.0, sigma_pixel=1.0, sigma_depth=10.0,
+                               max_iter=it)
+    assert out.dtype == np.float32 and out.shape == g["Twc"].shape
+    assert upd_err(out, g[f"calib_it{it}"], g["Twc"]) <= REL
+
+
+def test_gn_golden_variants(K, golden):
+    g = golden("gn_graph")
+    a = gargs(g)
+    assert upd_err(K.gauss_newton_rays(*a, max_iter=2, pin=2), g["rays_pin2"], g["Twc"]) <= REL
+    out = K.gauss_newton_calib(g["Twc"], g["Xs"], g["Cs"], g["K4"], g["ii"], g["jj"], g["idx"],
+                               g["valid"], g["Q"], tuple(int(v) for v in g["img_size"]),
+                               pixel_border=0, z_eps=0.0, sigma_pixel=1.0, sigma_depth=0.1, max_iter=2)
+    assert upd_err(out, g["calib_k4"], g["Twc"]) <= REL
+    # [...,1]-shaped Cs / valid / Q (gauss_newton.py:84-89)
+    out = K.gauss_newton_rays(g["Twc"], g["Xs"], g["Cs"][..., None], g["ii"], g["jj"], g["idx"],
+                              g["valid"][..., None], g["Q"][..., None], max_iter=2)
+    assert upd_err(out, g["rays_it2"], g["Twc"]) <= REL
+
+
+def test_gn_golden_random_generator(K, golden):
+    """the reference benchmark's own (incoherent, non-convergent) data: first iteration"""
+    g = golden("gn_random")
+    a = gargs(g)
+    assert upd_err(K.gauss_newton_rays(*a, max_iter=1), g["rays_it1"], g["Twc"]) <= REL
+    assert upd_err(K.gauss_newton_points(*a, max_iter=1), g["points_it1"], g["Twc"]) <= REL
+
+
+def test_gn_early_outs(K, golden):
+    g = golden("gn_graph")
+    e = golden("gn_early")
+    out = K.gauss_newton_rays(g["Twc"], g["Xs"], g["Cs"], g["ii"][:0], g["jj"][:0], g["idx"][:0],
+                              g["valid"][:0], g["Q"][:0])
+    assert np.array_equal(out, e["no_edges"])
+    out = K.gauss_newton_rays(*gargs(g), pin=5)
+    assert np.array_equal(out, e["pin_all"])
+    out = K.gauss_newton_points(*gargs(g), pin=7)
+    assert np.array_equal(out, g["Twc"])
+    # all matches invalid: H = 1e-6 I, g = 0 -> dx = 0 -> stop, poses unchanged
+    out = K.gauss_newton_rays(g["Twc"], g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"],
+                              np.zeros_like(g["valid"]), g["Q"])
+    assert np.array_equal(out, g["Twc"])
+
+
+@pytest.mark.parametrize("mode", ["rays", "points", "calib"])
+def test_gn_first_iteration_internals(K, oracle, synth, mode):
+    """H, g (fp64) and dx of iteration 1 against the oracle's, through the step-wise C ABI"""
+    import ctypes as C
+    import torch
+    from mast3r_slam_b200 import _lib
+    g = synth.make_graph(3, 8, 3, 48, 64, num_pts=2001)  # odd N: scalar tail paths
+    dev = torch.device("cuda", 0)
+    plan = K.GNPlan(g["ii"], g["jj"], 8, 2001, 1, dev)
+    kw = dict(sigma_pixel=1.0, sigma_depth=10.0) if mode == "calib" else {}
+    if mode == "calib":
+        params = K.make_params(_lib.GN_CALIB, 1, 1, 1e-4, 0.0, 1.5, 1.0, 10.0, g["K4"], g["img_size"], 0, 0.0)
+        ref, dbg = oracle.gauss_newton_calib(g["Twc"], g["Xs"], g["Cs"], g["K4"], g["ii"], g["jj"],
+                                             g["idx"], g["valid"], g["Q"], g["img_size"], max_iter=1,
+                                             debug=True, **kw)
+    elif mode == "rays":
+        params = K.make_params(_lib.GN_RAYS, 1, 1, 1e-4, 0.0, 1.5, 0.003)
+        ref, dbg = oracle.gauss_newton_rays(*gargs(g), max_iter=1, debug=True)
+    else:
+        params = K.make_params(_lib.GN_POINTS, 1, 1, 1e-4, 0.0, 1.5, 0.01)
+        ref, dbg = oracle.gauss_newton_points(*gargs(g), max_iter=1, debug=True)
+    t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a)).to(dev, dt)  # noqa: E731
+    Twc, Xs, Cs = t(g["Twc"], torch.float32), t(g["Xs"], torch.float32), t(g["Cs"], torch.float32)
+    idx, valid, Q = t(g["idx"], torch.int32), t(g["valid"].astype(np.uint8), torch.uint8), t(g["Q"], torch.float32)
+    lib = _lib.load()
+    p = lambda x: C.c_void_p(x.data_ptr())  # noqa: E731
+    _lib.check(lib.m3s_gn_set_poses(plan.handle, p(Twc), None))
+    _lib.check(lib.m3s_gn_accumulate(plan.handle, C.byref(params), p(Xs), p(Cs), p(idx), p(valid), p(Q),
+                                     0, plan.E, None))
+    _lib.check(lib.m3s_gn_assemble(plan.handle, None))
+    torch.cuda.synchronize()
+    H = plan.H().cpu().numpy()
+    gv = plan.g().cpu().numpy()
+    assert plan.F == dbg["F"] and H.shape == dbg["H"].shape
+    scale = np.abs(dbg["H"]).max()
+    assert np.abs(H - dbg["H"]).max() <= 1e-11 * scale
+    assert np.abs(gv - dbg["g"]).max() <= 1e-11 * np.abs(dbg["g"]).max()
+    _lib.check(lib.m3s_gn_solve_update(plan.handle, C.byref(params), None))
+    torch.cuda.synchronize()
+    dx = plan.dx().cpu().numpy()
+    assert np.abs(dx - dbg["dx"][0]).max() <= 1e-7 * np.abs(dbg["dx"][0]).max()
+    st = plan.status()
+    assert st["applied"] == 1 and not st["failed"]
+    out = torch.empty_like(Twc)
+    _lib.check(lib.m3s_gn_get_poses(plan.handle, p(out), None))
+    assert upd_err(out.cpu().numpy(), ref, g["Twc"]) <= REL
+
+
+def test_gn_edge_sharding_is_bitwise(K, synth):
+    """edge ranges accumulated separately and summed (the multi-GPU all-reduce) reproduce the
+    single-pass per-edge blocks bit for bit"""
+    import ctypes as C
+    import torch
+    from mast3r_slam_b200 import _lib
+    g = synth.make_graph(4, 6, 2, 32, 48)
+    dev = torch.device("cuda", 0)
+    n = g["Xs"].shape[1]
+    plan = K.GNPlan(g["ii"], g["jj"], 6, n, 1, dev)
+    params = K.make_params(_lib.GN_POINTS, 1, 1, 1e-4, 0.0, 1.5, 0.01)
+    t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a)).to(dev, dt)  # noqa: E731
+    Twc, Xs, Cs = t(g["Twc"], torch.float32), t(g["Xs"], torch.float32), t(g["Cs"], torch.float32)
+    idx, valid, Q = t(g["idx"], torch.int32), t(g["valid"].astype(np.uint8), torch.uint8), t(g["Q"], torch.float32)
+    lib = _lib.load()
+    p = lambda x: C.c_void_p(x.data_ptr())  # noqa: E731
+    _lib.check(lib.m3s_gn_set_poses(plan.handle, p(Twc), None))
+
+    def acc(b, e):
+        _lib.check(lib.m3s_gn_accumulate(plan.handle, C.byref(params), p(Xs), p(Cs), p(idx), p(valid),
+                                         p(Q), b, e, None))
+        torch.cuda.synchronize()
+        return plan.edge_blocks().clone()
+
+    full = acc(0, plan.E)
+    parts = acc(0, 5) + acc(5, 11) + acc(11, plan.E)
+    assert torch.equal(full, parts)
+    assert full.abs().sum() > 0
+
+
+@pytest.mark.parametrize("cfg", [(10, 3, 2048, "rays"), (40, 12, 600, "points"), (12, 4, 1500, "calib")])
+def test_gn_vs_oracle_graphs(K, oracle, synth, cfg):
+    """config-3-like graphs at reduced num_pts (the numpy oracle needs minutes per iteration at full
+    size); multi-panel Cholesky (dim up to 273)."""
+    nkf, loops, npts, mode = cfg
+    g = synth.make_graph(10 + nkf, nkf, loops, 96, 128, num_pts=npts)
+    if mode == "calib":
+        out = K.gauss_newton_calib(g["Twc"], g["Xs"], g["Cs"], g["K4"], g["ii"], g["jj"], g["idx"],
+                                   g["valid"], g["Q"], g["img_size"], sigma_depth=10.0, max_iter=10)
+        ref = oracle.gauss_newton_calib(g["Twc"], g["Xs"], g["Cs"], g["K4"], g["ii"], g["jj"], g["idx"],
+                                        g["valid"], g["Q"], g["img_size"], sigma_depth=10.0, max_iter=10)
+    else:
+        fn = "gauss_newton_" + mode
+        out = getattr(K, fn)(*gargs(g), max_iter=10)
+        ref = getattr(oracle, fn)(*gargs(g), max_iter=10)
+    assert upd_err(out, ref, g["Twc"]) <= REL
+    # and the solve moved the poses towards the ground truth
+    assert np.abs(out - g["Twc_gt"]).max() < 0.5 * np.abs(g["Twc"] - g["Twc_gt"]).max()
+
+
+def test_gn_200_keyframes(K, oracle, synth):
+    """BASELINE.json config 5 topology (200 KF, 1000 directed edges, dim 1393) at reduced num_pts"""
+    g = synth.make_graph(7, 200, 103, 48, 64, num_pts=512)
+    assert len(g["ii"]) == 1000
+    out = K.gauss_newton_points(*gargs(g), max_iter=3)
+    ref = oracle.gauss_newton_points(*gargs(g), max_iter=3)
+    assert upd_err(out, ref, g["Twc"]) <= REL
+
+
+def test_l2_global_opt_entry_points(K, oracle, synth):
+    from mast3r_slam_b200 import global_opt
+    g = synth.make_graph(2, 5, 1, 32, 48)
+    e = len(g["ii"]) // 2
+    # split the generator's interleaved two-way rows into the FactorGraph's one-way storage
+    fw, bw = slice(0, None, 2), slice(1, None, 2)
+    two = global_opt.prep_two_way_edges(g["ii"][fw], g["jj"][fw], g["idx"][fw], g["idx"][bw],
+                                        g["valid"][fw], g["valid"][bw], g["Q"][fw], g["Q"][bw])
+    assert len(two[0]) == 2 * e and np.array_equal(two[0][e:], g["jj"][fw])
+    out = global_opt.solve_GN_rays(g["Twc"], g["Xs"], g["Cs"], *two)
+    ref = oracle.gauss_newton_rays(g["Twc"], g["Xs"], g["Cs"], *two, sigma_ray=0.003, max_iter=10,
+                                   delta_thresh=1e-3)
+    assert upd_err(out, ref, g["Twc"]) <= REL
+    out = global_opt.solve_GN_calib(g["Twc"], g["Xs"], g["Cs"], g["K4"], *two, g["img_size"])
+    ref = oracle.gauss_newton_calib(g["Twc"], g["Xs"], g["Cs"], g["K4"], *two, g["img_size"],
+                                    sigma_pixel=1.0, sigma_depth=10.0, max_iter=10, delta_thresh=1e-3)
+    assert upd_err(out, ref, g["Twc"]) <= REL

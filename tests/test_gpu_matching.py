@@ -1,0 +1,224 @@
+"""GPU parity tests for the matching stages (run on the B200 box: pytest -m gpu).
+
+Every call goes through the C ABI (ctypes -> libm3s_b200.so).  Results are compared with the golden
+vectors produced by the reference itself and with the CPU oracle on seeded inputs.  The bar is
+bit-exact: positions (float32), validity and integer indices must be identical.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def K():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from mast3r_slam_b200 import kernels
+    assert kernels.is_available(), "CUDA extension not loaded"
+    return kernels
+
+
+@pytest.fixture(scope="module")
+def synth():
+    from mast3r_slam_b200 import synth as s
+    return s
+
+
+def test_iter_proj_golden_random(K, golden):
+    g = golden("iter_proj_random")
+    p, v = K.iter_proj(g["rays"], g["pts"], g["p_init"], 10, 1e-8, 1e-6)
+    assert p.dtype == np.float32 and v.dtype == np.bool_
+    assert np.array_equal(v, g["valid"])
+    assert np.array_equal(p, g["p"])
+
+
+@pytest.mark.parametrize("it", [1, 3, 10])
+def test_iter_proj_golden_scene(K, golden, it):
+    g = golden("iter_proj_scene")
+    p, v = K.iter_proj(g["rays"], g["pts"], g["p_init"], it, 1e-8, 1e-6)
+    assert np.array_equal(v, g[f"valid_{it}"])
+    assert np.array_equal(p, g[f"p_{it}"])
+
+
+def test_iter_proj_global_break(K, golden):
+    """kernels.py:239-241: the loop stops for ALL points once max ||delta|| < thresh."""
+    g = golden("iter_proj_break")
+    p, v = K.iter_proj(g["rays_same"], g["pts_same"], g["p0_same"], 10, 1e-8, 1e-6)
+    assert np.array_equal(p, g["p_same"]) and np.array_equal(v, g["valid_same"])
+    p, v = K.iter_proj(g["rays"], g["pts"], g["p_init"], 10, 1e-8, float(g["thresh"]))
+    assert np.array_equal(p, g["p"]) and np.array_equal(v, g["valid"])
+    # same inputs, tiny threshold: must NOT stop early (differs from the early-stopped result)
+    p10, _ = K.iter_proj(g["rays"], g["pts"], g["p_init"], 10, 1e-8, 0.0)
+    assert not np.array_equal(p10, g["p"])
+
+
+@pytest.mark.parametrize("shape", [(1, 33, 47, 1000), (3, 24, 40, 777), (2, 64, 64, 4096)])
+def test_iter_proj_vs_oracle_random(K, oracle, synth, shape):
+    b, h, w, n = shape
+    rays, pts, p0 = synth.reference_like_iter_proj(100 + n, b, h, w, n)
+    p0[:, :5, 0] -= 7.0
+    p0[:, 5:9, 1] += h
+    for it, lam in ((10, 1e-8), (4, 1e-3)):
+        p, v = K.iter_proj(rays, pts, p0, it, lam, 1e-6)
+        po, vo = oracle.iter_proj(rays, pts, p0, it, lam, 1e-6)
+        assert np.array_equal(v, vo)
+        assert np.array_equal(p, po)
+
+
+def test_iter_proj_edge_cases(K, oracle, synth):
+    rays, pts, p0 = synth.reference_like_iter_proj(5, 1, 16, 16, 64)
+    # zero iterations: clamp + validity of the initial positions only
+    p, v = K.iter_proj(rays, pts, p0, 0, 1e-8, 1e-6)
+    po, vo = oracle.iter_proj(rays, pts, p0, 0, 1e-8, 1e-6)
+    assert np.array_equal(p, po) and np.array_equal(v, vo)
+    # empty point set
+    p, v = K.iter_proj(rays, pts[:, :0], p0[:, :0], 10)
+    assert p.shape == (1, 0, 2) and v.shape == (1, 0)
+    # degenerate gradients (constant image): det clamps to 1e-10
+    flat = np.ones_like(rays)
+    p, v = K.iter_proj(flat, pts, p0, 3, 1e-8, 1e-6)
+    po, vo = oracle.iter_proj(flat, pts, p0, 3, 1e-8, 1e-6)
+    assert np.array_equal(p, po) and np.array_equal(v, vo)
+    # torch CUDA tensors in -> torch CUDA tensors out, same bits
+    import torch
+    pt, vt = K.iter_proj(torch.from_numpy(rays).cuda(), torch.from_numpy(pts).cuda(),
+                         torch.from_numpy(p0).cuda(), 10)
+    assert pt.is_cuda and vt.dtype == torch.bool
+    po, vo = oracle.iter_proj(rays, pts, p0, 10)
+    assert np.array_equal(pt.cpu().numpy(), po) and np.array_equal(vt.cpu().numpy(), vo)
+
+
+def test_prep_and_tail_vs_oracle(K, oracle, synth):
+    pair = synth.make_pair(2, 40, 56)
+    X11, X21 = pair["X11"][None], pair["X21"][None]
+    X11b = np.concatenate([X11, X11[:, ::-1].copy()])
+    X21b = np.concatenate([X21, X21[:, :, ::-1].copy()])
+    idx0 = np.random.default_rng(0).integers(0, 40 * 56, (2, 40 * 56)).astype(np.int32)
+    for idx in (None, idx0):
+        got = K.prep_for_iter_proj(X11b, X21b, idx)
+        ref = oracle.prep_for_iter_proj(X11b, X21b, idx)
+        for a, b in zip(got, ref):
+            assert np.array_equal(a, b)
+    rng = np.random.default_rng(1)
+    p1 = np.stack([rng.integers(-3, 60, (2, 40 * 56)), rng.integers(-3, 44, (2, 40 * 56))], -1).astype(np.int32)
+    vp = rng.random((2, 40 * 56)) < 0.8
+    idx, valid = K.match_tail(X11b, X21b, p1, vp, 0.1)
+    idx_o, valid_o = oracle.match_tail(X11b, X21b, p1, vp, 0.1)
+    assert idx.dtype == np.int32 and valid.shape == (2, 40 * 56, 1)
+    assert np.array_equal(idx, idx_o) and np.array_equal(valid, valid_o)
+
+
+@pytest.mark.parametrize("key", ["r3_d0", "r3_d2", "r1_d1", "r2_d3"])
+def test_refine_golden_dyadic(K, golden, key):
+    g = golden("refine_dyadic")
+    r, d = int(key[1]), int(key[4])
+    out = K.refine_matches(g["D11"], g["D21"], g["p1"], r, d)
+    assert out.dtype == np.int32
+    assert np.array_equal(out, g[key])
+
+
+def _near_tie_ok(D11, D21, a, b):
+    """rows where the two answers differ must be rounding-level ties of the fp32 score"""
+    bad = np.argwhere((a != b).any(-1))
+    for bi, n in bad:
+        q = D21[bi, n].astype(np.float64)
+        sa = q @ D11[bi, a[bi, n, 1], a[bi, n, 0]].astype(np.float64)
+        sb = q @ D11[bi, b[bi, n, 1], b[bi, n, 0]].astype(np.float64)
+        assert abs(sa - sb) <= 4 * np.finfo(np.float32).eps * max(abs(sa), abs(sb), 1.0), (bi, n, sa, sb)
+    return len(bad)
+
+
+def test_refine_golden_unit(K, golden):
+    g = golden("refine_unit")
+    out = K.refine_matches(g["D11"], g["D21"], g["p1"], 3, 2)
+    assert _near_tie_ok(g["D11"], g["D21"], out, g["r3_d2"]) <= 2
+    gf = golden("refine_floatp")
+    out = K.refine_matches(g["D11"], g["D21"][:, :50], gf["p1f"], 2, 0)
+    assert np.array_equal(out, gf["r2_d0"])
+
+
+@pytest.mark.parametrize("d", [24, 16, 32, 64, 20, 7])
+def test_refine_vs_oracle_dims(K, oracle, d):
+    """all descriptor widths (vectorised and generic kernels), dyadic values -> exact"""
+    rng = np.random.default_rng(d)
+    b, h, w, n = 2, 30, 45, 1200
+    D11 = (rng.integers(-128, 129, (b, h, w, d)) / 64.0).astype(np.float32)
+    D21 = (rng.integers(-128, 129, (b, n, d)) / 64.0).astype(np.float32)
+    p1 = np.stack([rng.integers(-4, w + 4, (b, n)), rng.integers(-4, h + 4, (b, n))], -1).astype(np.int32)
+    for r in (0, 1, 3, 5):
+        out = K.refine_matches(D11, D21, p1, r, 0)
+        ref = oracle.refine_matches(D11, D21, p1, r, 0)
+        assert np.array_equal(out, ref), (d, r)
+    # ties: constant descriptors -> the first candidate in (dy, dx) scan order wins
+    D11c = np.ones_like(D11)
+    out = K.refine_matches(D11c, D21, p1, 2, 0)
+    ref = oracle.refine_matches(D11c, D21, p1, 2, 0)
+    assert np.array_equal(out, ref)
+
+
+@pytest.mark.parametrize("desc", ["dyadic", "unit"])
+def test_match_pipeline_vs_oracle(K, oracle, synth, desc):
+    """matching.py:339-461 end to end in one C-ABI call, B=2"""
+    ps = synth.make_pairs([7, 8], 72, 96, 24, desc)
+    idx, valid = K.match_iterative_proj_device(ps["X11"], ps["X21"], ps["D11"], ps["D21"])
+    idx_o, valid_o = oracle.match_iterative_proj(ps["X11"], ps["X21"], ps["D11"], ps["D21"])
+    assert idx.shape == (2, 72 * 96) and valid.shape == (2, 72 * 96, 1)
+    if desc == "dyadic":
+        assert np.array_equal(idx, idx_o) and np.array_equal(valid, valid_o)
+    else:
+        # non-dyadic scores: summation order (FMA chain vs the oracle's separate ops) may flip
+        # rounding-level ties only
+        same = idx == idx_o
+        assert (~same).mean() < 1e-3
+        assert np.array_equal(valid[same], valid_o[same])
+    # with an initial correspondence and without refinement
+    idx0 = idx_o.copy()
+    a = K.match_iterative_proj_device(ps["X11"], ps["X21"], ps["D11"], ps["D21"], idx0, radius=0)
+    b = oracle.match_iterative_proj(ps["X11"], ps["X21"], ps["D11"], ps["D21"], idx0, radius=0)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+def test_l2_match_entry_point(K, oracle, synth):
+    from mast3r_slam_b200 import matching
+    from mast3r_slam_b200.config import set_config
+    ps = synth.make_pairs([3], 48, 64)
+    with pytest.raises(NotImplementedError):
+        matching.match(ps["X11"], ps["X21"], ps["D11"], ps["D21"])
+    set_config({"matching": {"use_simple": False}})
+    try:
+        idx, valid = matching.match(ps["X11"], ps["X21"], ps["D11"], ps["D21"])
+    finally:
+        set_config({})
+    idx_o, valid_o = oracle.match_iterative_proj(ps["X11"], ps["X21"], ps["D11"], ps["D21"],
+                                                 radius=3, dilation_max=2)
+    assert np.array_equal(idx, idx_o) and np.array_equal(valid, valid_o)
+
+
+def test_full_size_config1(K, oracle, synth):
+    """BASELINE.json config 1: one 512x384 pair, D=24, 10 iterations, radius 3 -- bit-exact against
+    the oracle at full size, plus size-independent properties."""
+    pair = synth.make_pair(0, 384, 512, 24, "dyadic")
+    X11, X21, D11, D21 = (pair[k][None] for k in ("X11", "X21", "D11", "D21"))
+    rays, pts, p0 = K.prep_for_iter_proj(X11, X21, None)
+    ro, po_, p0o = oracle.prep_for_iter_proj(X11, X21, None)
+    assert np.array_equal(rays, ro) and np.array_equal(pts, po_) and np.array_equal(p0, p0o)
+    p, v = K.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6)
+    po, vo = oracle.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6)
+    assert np.array_equal(p, po) and np.array_equal(v, vo)
+    p1 = K.refine_matches(D11.reshape(1, 384, 512, 24), D21.reshape(1, -1, 24), p.astype(np.int32), 3, 0)
+    p1o = oracle.refine_matches(D11, D21.reshape(1, -1, 24), p.astype(np.int32), 3, 0)
+    assert np.array_equal(p1, p1o)
+    idx, valid = K.match_iterative_proj_device(X11, X21, D11, D21)
+    idx_o, valid_o = oracle.match_iterative_proj(X11, X21, D11, D21)
+    assert np.array_equal(idx, idx_o) and np.array_equal(valid, valid_o)
+    # properties: refined positions stay inside the window and inside the image; idempotent centre
+    c = p.astype(np.int32)
+    assert (np.abs(p1 - c) <= 3).all()
+    assert (p1[..., 0] >= 0).all() and (p1[..., 0] < 512).all() and (p1[..., 1] < 384).all()
+    # most matches recover the true flow to within the refinement window
+    flow = pair["flow_uv"].reshape(-1, 2)
+    ok = valid[0, :, 0]
+    err = np.abs(p[0][ok] - flow[ok]).max(-1)
+    assert np.median(err) < 0.5 and ok.mean() > 0.9
