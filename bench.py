@@ -1,0 +1,409 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the hot path (contract in the task statement).
+
+    python bench.py --gpus N --steps K --warmup W            # our CUDA path
+    python bench.py --impl reference --gpus N ...            # the reference's CPU path (oracle port)
+
+Headline (BASELINE.json `metric`): matched px/s for iter_proj + refine_matches at 512x384, D=24,
+10 LM iterations, radius 3, on a batch of 64 synthetic frame pairs per GPU (config 2; weak scaling:
+pairs are independent, no data-path collective).  A "step" is one pass of iter_proj + refine_matches
+over the whole 64-pair batch with all inputs resident in HBM (3.1 GB per step: far larger than the
+126 MB L2, so every step streams from HBM).  The same JSON line carries:
+  * `e2e`       -- the same metric through the public operator API with inputs in pinned HOST
+                   memory: per step H2D of all five inputs, both kernels, D2H of the refined
+                   positions and validity.
+  * `roofline`  -- for the dominant kernel: algorithmic bytes per launch / CUDA-event duration
+                   against the measured HBM copy bandwidth (MEASURED_PEAKS.json).
+  * `cpu_baseline` -- the CPU oracle (port of the reference's numpy path, all host threads) timed
+                   on a bounded sample of the same batch in the same run (rank 0, N=1 only).
+  * `gn`        -- the second half of BASELINE.json's metric: Gauss-Newton iterations/s on the
+                   200-keyframe / 1000-edge graph (config 5) at full 196 608 points per keyframe,
+                   gauss_newton_points, edges sharded over the N ranks with one NCCL all-reduce of
+                   the packed (H, g) blocks per iteration (strong scaling of one fixed graph).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H, W, D = 384, 512, 24
+NPIX = H * W
+PAIRS_PER_GPU = 64
+MAX_ITER, LAMBDA, THRESH, RADIUS = 10, 1e-8, 1e-6, 3
+ALG_BYTES_ITER_PROJ = 36 + 12 + 8 + 8 + 1        # rays + target + p_init in, p + valid out
+ALG_BYTES_REFINE = 96 + 96 + 8 + 8               # D11 + D21 + p in, p1 out
+ALG_BYTES_PATH = 257                             # fused iter_proj+refine
+GN_KF, GN_LOOPS = 200, 103
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            d = json.load(open(p))
+            return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms",
+                 "200", "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
+                text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            pass
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for k, nm in enumerate(names):
+                    if r[5 + k].lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                continue
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_oracle_rate(host, n_pairs_budget_s=12.0, threads=None):
+    """Time the CPU oracle (C port of the reference's numpy path) on a bounded sample of the batch.
+    Returns (px_per_s, cores, sample description)."""
+    from oracle import oracle
+    oracle.build()
+    if threads:
+        oracle.set_threads(threads)
+    cores = oracle.num_threads()
+
+    def run(k):
+        t0 = time.perf_counter()
+        p, _ = oracle.iter_proj(host["rays"][:k], host["pts"][:k], host["p0"][:k], MAX_ITER, LAMBDA, THRESH)
+        oracle.refine_matches(host["D11"][:k], host["D21"][:k], p.astype("int32"), RADIUS, 0)
+        return time.perf_counter() - t0
+
+    t1 = run(1)
+    k = int(max(1, min(host["rays"].shape[0], n_pairs_budget_s / max(t1, 1e-3))))
+    t = run(k) if k > 1 else t1
+    return k * NPIX / t, cores, f"{k} of the {host['rays'].shape[0]} pairs (first k), iter_proj+refine_matches, {t:.2f} s"
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pairs", type=int, default=PAIRS_PER_GPU, help="pairs per GPU per step")
+    ap.add_argument("--no-gn", action="store_true", help="skip the 200-keyframe Gauss-Newton leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--gn-iters", type=int, default=5)
+    ap.add_argument("--desc", default="dyadic")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+
+    import numpy as np
+    import torch
+    from mast3r_slam_b200 import _lib, dist as mdist, kernels, synth
+
+    rank, local_rank, world = mdist.init_from_env()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    lib = _lib.load()
+    peak, peak_src = load_peaks()
+    B = args.pairs
+
+    # ---- workload: config 2, seeds rank*B .. rank*B+B-1 (weak scaling: B pairs per GPU) ----------
+    pairs = synth.make_pairs_torch(range(rank * B, rank * B + B), dev, H, W, D, args.desc)
+    rays, pts, p0 = kernels.prep_for_iter_proj(pairs["X11"], pairs["X21"], None)
+    D11 = pairs["D11"]
+    D21 = pairs["D21"].reshape(B, NPIX, D)
+    del pairs
+    torch.cuda.synchronize()
+
+    def step_device():
+        p, valid = kernels.iter_proj(rays, pts, p0, MAX_ITER, LAMBDA, THRESH)
+        p1 = kernels.refine_matches(D11, D21, p, RADIUS, 0)
+        return p1, valid
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    stream = torch.cuda.current_stream(dev)
+    barrier()
+    t_wall0 = time.perf_counter()
+    for k in range(args.steps):
+        ev[k][0].record(stream)
+        p, valid = kernels.iter_proj(rays, pts, p0, MAX_ITER, LAMBDA, THRESH)
+        ev[k][1].record(stream)
+        p1 = kernels.refine_matches(D11, D21, p, RADIUS, 0)
+        ev[k][2].record(stream)
+    torch.cuda.synchronize()
+    t_wall = time.perf_counter() - t_wall0
+    t_total_ms = ev[0][0].elapsed_time(ev[-1][2])
+    t_ip_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / args.steps
+    t_rf_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    t_max_ms = mdist.max_over_ranks(t_total_ms, dev)
+    ms_per_step = t_max_ms / args.steps
+    value = world * B * NPIX / (ms_per_step * 1e-3)
+
+    # ---- roofline of the dominant kernel (per launch = one 64-pair batch) ------------------------
+    units = B * NPIX
+    kinfo = {
+        "iter_proj_kernel": {"ms": t_ip_ms, "alg_bytes": ALG_BYTES_ITER_PROJ * units},
+        "refine_kernel": {"ms": t_rf_ms, "alg_bytes": ALG_BYTES_REFINE * units},
+    }
+    for v in kinfo.values():
+        v["gbs"] = v["alg_bytes"] / (v["ms"] * 1e-3) / 1e9
+    dom = max(kinfo, key=lambda k: kinfo[k]["ms"])
+    path_gbs = ALG_BYTES_PATH * units / ((t_ip_ms + t_rf_ms) * 1e-3) / 1e9
+    roofline = {
+        "bound": "hbm", "kernel": dom, "achieved": round(kinfo[dom]["gbs"], 1), "peak": peak,
+        "unit": "GB/s", "frac": round(kinfo[dom]["gbs"] / peak, 4), "traffic": None,
+        "peak_source": peak_src,
+        "kernels": {k: {"ms_per_launch": round(v["ms"], 4), "alg_bytes_per_launch": v["alg_bytes"],
+                        "achieved_gbs": round(v["gbs"], 1), "frac": round(v["gbs"] / peak, 4)}
+                    for k, v in kinfo.items()},
+        "path": {"alg_bytes_per_px": ALG_BYTES_PATH, "achieved_gbs": round(path_gbs, 1),
+                 "frac": round(path_gbs / peak, 4)},
+    }
+
+    # ---- e2e: pinned host inputs -> H2D -> both kernels -> D2H of positions + validity -----------
+    e2e = None
+    host = None
+    if not args.no_e2e:
+        hp = {k: torch.empty(t.shape, dtype=t.dtype, pin_memory=True).copy_(t)
+              for k, t in (("rays", rays), ("pts", pts), ("p0", p0), ("D11", D11), ("D21", D21))}
+        out_p1 = torch.empty((B, NPIX, 2), dtype=torch.int32, pin_memory=True)
+        out_v = torch.empty((B, NPIX), dtype=torch.bool, pin_memory=True)
+        h2d = sum(t.numel() * t.element_size() for t in hp.values())
+        d2h = out_p1.numel() * 4 + out_v.numel()
+
+        def step_e2e():
+            d = {k: t.to(dev, non_blocking=True) for k, t in hp.items()}
+            p, valid = kernels.iter_proj(d["rays"], d["pts"], d["p0"], MAX_ITER, LAMBDA, THRESH)
+            p1 = kernels.refine_matches(d["D11"], d["D21"], p, RADIUS, 0)
+            out_p1.copy_(p1, non_blocking=True)
+            out_v.copy_(valid, non_blocking=True)
+
+        e_steps = max(2, min(args.steps, 5))
+        step_e2e()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(e_steps):
+            step_e2e()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        t_e2e_ms = mdist.max_over_ranks(e0.elapsed_time(e1), dev) / e_steps
+        e2e = {"value": world * B * NPIX / (t_e2e_ms * 1e-3), "unit": "px/s",
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": round(t_e2e_ms, 3),
+               "steps": e_steps}
+        host = {k: v.numpy() for k, v in hp.items()}
+
+    # ---- CPU baseline (rank 0, N = 1 only) -------------------------------------------------------
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        if host is None:
+            host = {k: t.cpu().numpy() for k, t in (("rays", rays), ("pts", pts), ("p0", p0), ("D11", D11), ("D21", D21))}
+        v, cores, sample = cpu_oracle_rate(host)
+        cpu_baseline = {"value": v, "unit": "px/s", "cores": cores, "kind": "port", "sample": sample}
+    del rays, pts, p0, D11, D21
+    host = None
+    torch.cuda.empty_cache()
+
+    # ---- GN leg: 200-KF graph, edges sharded over ranks ------------------------------------------
+    gn = None
+    if not args.no_gn:
+        gn = gn_leg(args, rank, world, dev, peak)
+
+    if rank == 0:
+        line = {
+            "metric": "matched_px_per_s (iter_proj+refine_matches, 512x384, D=24, 10 it, r=3)",
+            "value": value, "unit": "px/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32 (+f64 bilinear blend)",
+            "data": "synthetic",
+            "config": {"workload": f"config 2: batch of {B} synthetic 512x384 frame pairs per GPU, "
+                                   "desc dim 24, iter_proj (10 iters) + refine_matches radius 3",
+                       "pairs_per_gpu": B, "H": H, "W": W, "D": D, "descriptors": args.desc,
+                       "l2_policy": "inputs larger than L2 (3.1 GB per step vs 126 MB L2)",
+                       "parallelism": f"pairs x{world} (no collective)"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": 4 * args.steps, "roofline": roofline,
+            "cpu_baseline": cpu_baseline, "gn": gn, "wall_s_timed_region": round(t_wall, 4),
+        }
+        print(json.dumps(line))
+    if world > 1:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
+
+
+def gn_leg(args, rank, world, dev, peak):
+    """Config 5: gauss_newton_points on a 200-KF / 1000-directed-edge graph, N = 196 608."""
+    import ctypes as C
+    import torch
+    from mast3r_slam_b200 import _lib, dist as mdist, kernels, synth
+    e_total = 2 * ((GN_KF - 1) + (GN_KF - 2) + GN_LOOPS)
+    eb, ee = mdist.shard_edge_range(e_total, rank, world, 2)
+    g = synth.make_graph_torch(dev, 0, GN_KF, GN_LOOPS, H, W, edge_range=(eb, ee))
+    assert len(g["ii"]) == e_total
+    sg = mdist.ShardedGaussNewton(g["ii"], g["jj"], GN_KF, NPIX, 1, dev, eb, ee)
+    params = kernels.make_params(_lib.GN_POINTS, args.gn_iters, 1, 0.0, 0.0, 1.5, 0.01)
+    Twc = torch.from_numpy(g["Twc"]).to(dev)
+    lib = _lib.load()
+    stream = torch.cuda.current_stream(dev)
+    st = C.c_void_p(stream.cuda_stream)
+
+    def reset():
+        _lib.check(lib.m3s_gn_set_poses(sg.plan.handle, C.c_void_p(Twc.data_ptr()), st))
+
+    def sync():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    reset()
+    sg.iterate(params, g["Xs"], g["Cs"], g["idx"], g["valid"], g["Q"], 2)  # warm-up
+    sync()
+    reset()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync()
+    e0.record(stream)
+    sg.iterate(params, g["Xs"], g["Cs"], g["idx"], g["valid"], g["Q"], args.gn_iters)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = mdist.max_over_ranks(e0.elapsed_time(e1), dev) / args.gn_iters
+    status = sg.plan.status()
+    # accumulate kernel alone (dominant): event-timed on its stream
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reset()
+    torch.cuda.synchronize()
+    a0.record(stream)
+    p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    for _ in range(3):
+        _lib.check(lib.m3s_gn_accumulate(
+            sg.plan.handle, C.byref(params), p(g["Xs"]), p(g["Cs"]), sg._local_base(g["idx"], NPIX, 4),
+            sg._local_base(g["valid"], NPIX, 1), sg._local_base(g["Q"], NPIX, 4), eb, ee, st))
+    a1.record(stream)
+    torch.cuda.synchronize()
+    acc_ms = a0.elapsed_time(a1) / 3
+    ne = ee - eb
+    alg = 9 * ne * NPIX + 16 * GN_KF * NPIX + (7 * 199) ** 2 * 8
+    out = torch.empty_like(Twc)
+    _lib.check(lib.m3s_gn_get_poses(sg.plan.handle, p(out), st))
+    torch.cuda.synchronize()
+    err0 = float(abs(g["Twc"] - g["Twc_gt"]).max())
+    return {
+        "metric": "gn_iters_per_s (gauss_newton_points, 200 KF / 1000 directed edges, 196608 pts/KF)",
+        "value": 1e3 / ms, "unit": "iter/s", "ms_per_iter": round(ms, 4), "iters_timed": args.gn_iters,
+        "n_gpus": world, "scaling": "strong (edges sharded, 1 all-reduce of packed H,g per iteration)",
+        "edges_this_rank": ne, "dim": sg.plan.dim,
+        "accumulate_ms": round(acc_ms, 4), "solve_update_ms": round(ms - acc_ms, 4),
+        "roofline": {"bound": "hbm", "kernel": "gn_accum_kernel", "alg_bytes_per_launch": alg,
+                     "achieved": round(alg / (acc_ms * 1e-3) / 1e9, 1), "peak": peak, "unit": "GB/s",
+                     "frac": round(alg / (acc_ms * 1e-3) / 1e9 / peak, 4)},
+        "status": status,
+        "pose_err_before": err0,
+    }
+
+
+def reference_arm(args, rank, world):
+    """The reference's own CPU implementation of the path (its numpy fallbacks, which is what its
+    dispatcher executes without Metal), as the C/OpenMP port in oracle/ on all host threads.  The
+    reference is pure Python and does not travel to the GPU box; oracle/ is pinned to it by golden
+    vectors (tests/golden).  Each step = a bounded sample (`--pairs`, default 2) of the 64-pair
+    workload.  Rank 0 alone runs."""
+    if rank != 0:
+        return
+    import numpy as np
+    from mast3r_slam_b200 import synth
+    from oracle import oracle
+    oracle.build()
+    k = args.pairs if args.pairs != PAIRS_PER_GPU else 8
+    ps = synth.make_pairs(range(k), H, W, D, args.desc)
+    rays, pts, p0 = oracle.prep_for_iter_proj(ps["X11"], ps["X21"], None)
+    D11, D21 = ps["D11"], ps["D21"].reshape(k, NPIX, D)
+    cores = oracle.num_threads()
+
+    def step():
+        p, _ = oracle.iter_proj(rays, pts, p0, MAX_ITER, LAMBDA, THRESH)
+        oracle.refine_matches(D11, D21, p.astype(np.int32), RADIUS, 0)
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    t = time.perf_counter() - t0
+    v = k * NPIX * args.steps / t
+    sample = f"{k} of the 64 pairs per step, iter_proj+refine_matches, {t / args.steps:.3f} s/step"
+    print(json.dumps({
+        "impl": "reference",
+        "metric": "matched_px_per_s (iter_proj+refine_matches, 512x384, D=24, 10 it, r=3)",
+        "value": v, "unit": "px/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(1e3 * t / args.steps, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32 (+f64 bilinear blend)", "data": "synthetic",
+        "config": {"workload": "config 2: batch of 64 synthetic 512x384 frame pairs per GPU, desc dim "
+                               "24, iter_proj (10 iters) + refine_matches radius 3",
+                   "sample_pairs_per_step": k, "H": H, "W": W, "D": D, "descriptors": args.desc},
+        "cpu_baseline": {"value": v, "unit": "px/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "px/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+if __name__ == "__main__":
+    main()

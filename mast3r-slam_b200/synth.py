@@ -243,3 +243,114 @@ def reference_like_gn(seed, num_kf=10, num_pts=500, num_edges=15):
     valid = rng.random((num_edges, num_pts)) > 0.3
     Q = (rng.random((num_edges, num_pts)) * 3 + 1).astype(np.float32)
     return Twc, Xs, Cs, ii, jj, idx, valid, Q
+
+
+# ---------------------------------------------------------------------------------------------
+# device-side generators for full-size benchmark workloads (same scene model, torch on the GPU)
+# ---------------------------------------------------------------------------------------------
+def make_pairs_torch(seeds, device, h=384, w=512, d=24, desc="dyadic", noise=1e-3):
+    """Config 2 (64 pairs): dict of CUDA tensors X11, X21 [B,H,W,3], D11, D21 [B,H,W,d], float32.
+    Same scene model as make_pair; generated on the device so full-size batches take seconds."""
+    import torch
+    fx, fy, cx0, cy0 = intrinsics(h, w)
+    vv, uu = torch.meshgrid(torch.arange(h, dtype=torch.float64, device=device),
+                            torch.arange(w, dtype=torch.float64, device=device), indexing="ij")
+
+    def surface(u, v):
+        z = 2.0 + 0.5 * torch.sin(2 * np.pi * u / w) * torch.cos(2 * np.pi * v / h) + 0.3 * (u / w)
+        return torch.stack([(u - cx0) / fx * z, (v - cy0) / fy * z, z], -1)
+
+    out = {k: [] for k in ("X11", "X21", "D11", "D21")}
+    cell = 6
+    gh, gw = h // cell + 3, w // cell + 3
+    for seed in seeds:
+        gen = torch.Generator(device=device)
+        gen.manual_seed(1000 + int(seed))
+        rng = np.random.default_rng(1000 + int(seed))
+        s = 1.0 + 0.01 * rng.uniform(-1, 1)
+        th = 0.01 * rng.uniform(-1, 1)
+        t = rng.uniform(-3.0, 3.0, size=2)
+        cx, cy = (w - 1) / 2.0, (h - 1) / 2.0
+        du, dv = uu - cx, vv - cy
+        u2 = cx + s * (np.cos(th) * du - np.sin(th) * dv) + t[0]
+        v2 = cy + s * (np.sin(th) * du + np.cos(th) * dv) + t[1]
+        X11 = surface(uu, vv)
+        X21 = surface(u2, v2) + noise * torch.randn((h, w, 3), generator=gen, device=device, dtype=torch.float64)
+        coarse = torch.randn((gh, gw, d), generator=gen, device=device, dtype=torch.float64)
+
+        def field(u, v):
+            gu = torch.clamp(u / cell + 1.0, 0, gw - 1.001)
+            gv = torch.clamp(v / cell + 1.0, 0, gh - 1.001)
+            x0, y0 = gu.floor().long(), gv.floor().long()
+            fx_, fy_ = (gu - x0)[..., None], (gv - y0)[..., None]
+            return ((1 - fx_) * (1 - fy_) * coarse[y0, x0] + (1 - fx_) * fy_ * coarse[y0 + 1, x0]
+                    + fx_ * (1 - fy_) * coarse[y0, x0 + 1] + fx_ * fy_ * coarse[y0 + 1, x0 + 1])
+
+        D11 = field(uu, vv) + 0.15 * torch.randn((h, w, d), generator=gen, device=device, dtype=torch.float64)
+        D21 = field(u2, v2) + 0.15 * torch.randn((h, w, d), generator=gen, device=device, dtype=torch.float64)
+        if desc == "dyadic":
+            D11 = torch.clamp(torch.round(D11 * 64.0) / 64.0, -2.0, 2.0)
+            D21 = torch.clamp(torch.round(D21 * 64.0) / 64.0, -2.0, 2.0)
+        else:
+            D11 = D11 / D11.norm(dim=-1, keepdim=True)
+            D21 = D21 / D21.norm(dim=-1, keepdim=True)
+        for k, v in (("X11", X11), ("X21", X21), ("D11", D11), ("D21", D21)):
+            out[k].append(v.float())
+    return {k: torch.stack(v).contiguous() for k, v in out.items()}
+
+
+def make_graph_torch(device, seed=0, num_kf=200, num_loops=103, h=384, w=512, noise=1e-3,
+                     sigma_t=0.02, sigma_w=0.01, sigma_s=0.01, valid_frac=0.85, edge_range=None):
+    """Config 3 / 5 at full num_pts, generated on the device.  Same model as make_graph (poses and
+    topology come from the same numpy stream, so every rank builds the identical graph).
+    `edge_range=(b, e)`: only materialise idx/valid/Q rows of directed edges [b, e) (edge-sharded
+    ranks), other rows are left out; ii/jj always cover the whole graph.
+    Returns dict(Twc, Twc_gt [K,8] f32 numpy; ii, jj numpy; Xs [K,N,3], Cs [K,N], idx, valid (uint8),
+    Q CUDA tensors; K4; img_size)."""
+    import torch
+    rng = np.random.default_rng(5000 + seed)
+    fx, fy, cx0, cy0 = intrinsics(h, w)
+    vv, uu = torch.meshgrid(torch.arange(h, dtype=torch.float64, device=device),
+                            torch.arange(w, dtype=torch.float64, device=device), indexing="ij")
+    z = 2.0 + 0.5 * torch.sin(2 * np.pi * uu / w) * torch.cos(2 * np.pi * vv / h) + 0.3 * (uu / w)
+    P = torch.stack([(uu - cx0) / fx * z, (vv - cy0) / fy * z, z], -1).reshape(-1, 3)
+    n = P.shape[0]
+    gen = torch.Generator(device=device)
+    gen.manual_seed(5000 + seed)
+    Twc_gt = np.zeros((num_kf, 8))
+    Twc = np.zeros((num_kf, 8))
+    Xs = torch.empty((num_kf, n, 3), dtype=torch.float32, device=device)
+    shifts = np.zeros(num_kf, np.int64)
+    base = torch.arange(n, device=device)
+    for k in range(num_kf):
+        if k == 0:
+            t, q, s = np.zeros(3), np.array([0, 0, 0, 1.0]), 1.0
+        else:
+            t = 0.05 * rng.standard_normal(3)
+            q = _quat_from_rotvec(0.03 * rng.standard_normal(3))
+            s = 1.0 + 0.02 * rng.uniform(-1, 1)
+            shifts[k] = int(rng.integers(-3 * w, 3 * w))
+        Twc_gt[k] = np.concatenate([t, q, [s]])
+        R = torch.from_numpy(_rotmat(q)).to(device)
+        Pk = P[(base + int(shifts[k])) % n]
+        Xk = (Pk - torch.from_numpy(t).to(device)) @ R / s
+        Xs[k] = (Xk + noise * torch.randn((n, 3), generator=gen, device=device, dtype=torch.float64)).float()
+        if k == 0:
+            Twc[k] = Twc_gt[k]
+        else:
+            dq = _quat_from_rotvec(sigma_w * rng.standard_normal(3))
+            Twc[k] = np.concatenate([t + sigma_t * rng.standard_normal(3), _quat_mul(dq, q),
+                                     [s * np.exp(sigma_s * rng.standard_normal())]])
+    ii, jj = graph_edges(num_kf, num_loops, rng)
+    e = len(ii)
+    eb, ee = (0, e) if edge_range is None else edge_range
+    ne = ee - eb
+    idx = torch.empty((ne, n), dtype=torch.int32, device=device)
+    for r, k in enumerate(range(eb, ee)):
+        idx[r] = ((base + int(shifts[jj[k]] - shifts[ii[k]])) % n).int()
+    valid = (torch.rand((ne, n), generator=gen, device=device) < valid_frac).to(torch.uint8)
+    Q = 1.2 + 2.8 * torch.rand((ne, n), generator=gen, device=device)
+    Cs = 1.0 + 10.0 * torch.rand((num_kf, n), generator=gen, device=device)
+    return dict(Twc=Twc.astype(np.float32), Twc_gt=Twc_gt.astype(np.float32), Xs=Xs, Cs=Cs, ii=ii, jj=jj,
+                idx=idx, valid=valid, Q=Q, K4=np.array([fx, fy, cx0, cy0], np.float32), img_size=(w, h),
+                edge_range=(eb, ee))
