@@ -6,8 +6,22 @@
 // candidates skipped, centre kept when no candidate is inside the image.
 //
 // Scores are fp32 sums over D products.  The reference's np.dot is BLAS sdot whose summation order
-// is unspecified, so FMA accumulation (k ascending) is used here; for descriptors on a dyadic grid
-// every order is exact and the argmax is bit-exact unconditionally.
+// is unspecified; every kernel here uses ONE canonical order -- four component-wise FMA chains over
+// the float4 chunks, combined as (x + y) + (z + w) -- so all code paths agree bit for bit with each
+// other; for descriptors on a dyadic grid every order is exact and the argmax equals the
+// reference's unconditionally.
+//
+// Two implementations:
+//  * refine_tiled_kernel (full-frame matching, N == H*W, D == 24, r <= 3): the hot one.
+//    CTA = 32 x 16 queries (128 threads, 4 queries per thread stacked in y, lanes along x).  The
+//    candidate neighbourhood of the whole tile (40 x 24 pixels of D11) is staged once in shared
+//    memory (112-B pixel pitch => conflict-free LDS.128 across lanes); each candidate descriptor a
+//    thread loads is reused by up to 4 queries from registers (FFMA2 packed FMAs).  A query whose
+//    window does not fit the staged tile (incoherent flow) takes the generic global-memory path,
+//    so the result never depends on the tiling.
+//  * refine_kernel_vec / _generic: one thread per query straight from global memory/L1 (any N, D, r).
+#include <limits.h>
+
 #include "m3s_common.cuh"
 
 namespace m3s {
@@ -22,7 +36,39 @@ __device__ __forceinline__ int2 load_center(const float* p1, long long t) {
     return make_int2((int)f.x, (int)f.y);  // astype(int32): truncation toward zero
 }
 
-// One thread per query; query descriptor in registers (D4 float4), candidates through L1.
+struct Acc4 {
+    float2 xy, zw;
+    __device__ __forceinline__ Acc4() : xy(make_float2(0.f, 0.f)), zw(make_float2(0.f, 0.f)) {}
+    __device__ __forceinline__ void fma4(const float4& a, const float4& b) {
+        xy = __ffma2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y), xy);
+        zw = __ffma2_rn(make_float2(a.z, a.w), make_float2(b.z, b.w), zw);
+    }
+    __device__ __forceinline__ float sum() const { return (xy.x + xy.y) + (zw.x + zw.y); }
+};
+
+// generic per-query scan from global memory (canonical summation order)
+template <int D4>
+__device__ __forceinline__ void scan_global(const float4* __restrict__ img, const float4 (&q)[D4],
+                                            int cx, int cy, int radius, int H, int W, int& bx,
+                                            int& by) {
+    float best = -INFINITY;
+    bx = cx;
+    by = cy;
+    const int y_lo = max(cy - radius, 0), y_hi = min(cy + radius, H - 1);
+    const int x_lo = max(cx - radius, 0), x_hi = min(cx + radius, W - 1);
+    for (int ny = y_lo; ny <= y_hi; ++ny) {
+        const float4* __restrict__ row = img + ((size_t)ny * W) * D4;
+        for (int nx = x_lo; nx <= x_hi; ++nx) {
+            const float4* __restrict__ cd = row + (size_t)nx * D4;
+            Acc4 a;
+#pragma unroll
+            for (int k = 0; k < D4; ++k) a.fma4(q[k], __ldg(cd + k));
+            const float sc = a.sum();
+            if (sc > best) { best = sc; bx = nx; by = ny; }
+        }
+    }
+}
+
 template <int D4, typename PT>
 __global__ void __launch_bounds__(kRefineThreads)
 refine_kernel_vec(const float* __restrict__ D11, const float* __restrict__ D21,
@@ -38,31 +84,12 @@ refine_kernel_vec(const float* __restrict__ D11, const float* __restrict__ D21,
 #pragma unroll
     for (int k = 0; k < D4; ++k) q[k] = __ldg(qp + k);
     const int2 c = load_center(p1, t);
-    float best = -INFINITY;
-    int bx = c.x, by = c.y;
-    // clip the window to the image once: equivalent to skipping OOB candidates
-    const int y_lo = max(c.y - radius, 0), y_hi = min(c.y + radius, H - 1);
-    const int x_lo = max(c.x - radius, 0), x_hi = min(c.x + radius, W - 1);
-    for (int ny = y_lo; ny <= y_hi; ++ny) {
-        const float4* __restrict__ row = img + ((size_t)ny * W) * D4;
-        for (int nx = x_lo; nx <= x_hi; ++nx) {
-            const float4* __restrict__ cd = row + (size_t)nx * D4;
-            float sc = 0.0f;
-#pragma unroll
-            for (int k = 0; k < D4; ++k) {
-                const float4 v = __ldg(cd + k);
-                sc = fmaf(q[k].x, v.x, sc);
-                sc = fmaf(q[k].y, v.y, sc);
-                sc = fmaf(q[k].z, v.z, sc);
-                sc = fmaf(q[k].w, v.w, sc);
-            }
-            if (sc > best) { best = sc; bx = nx; by = ny; }
-        }
-    }
+    int bx, by;
+    scan_global<D4>(img, q, c.x, c.y, radius, H, W, bx, by);
     reinterpret_cast<int2*>(p1_out)[t] = make_int2(bx, by);
 }
 
-// Any descriptor dimension (scalar loads).
+// Any descriptor dimension (scalar loads; same canonical order: component j = k % 4).
 template <typename PT>
 __global__ void __launch_bounds__(kRefineThreads)
 refine_kernel_generic(const float* __restrict__ D11, const float* __restrict__ D21,
@@ -81,12 +108,159 @@ refine_kernel_generic(const float* __restrict__ D11, const float* __restrict__ D
     for (int ny = y_lo; ny <= y_hi; ++ny) {
         for (int nx = x_lo; nx <= x_hi; ++nx) {
             const float* __restrict__ cd = img + ((size_t)ny * W + nx) * D;
-            float sc = 0.0f;
-            for (int k = 0; k < D; ++k) sc = fmaf(__ldg(qp + k), __ldg(cd + k), sc);
+            float a[4] = {0.f, 0.f, 0.f, 0.f};
+            for (int k = 0; k < D; ++k) a[k & 3] = fmaf(__ldg(qp + k), __ldg(cd + k), a[k & 3]);
+            const float sc = (a[0] + a[1]) + (a[2] + a[3]);
             if (sc > best) { best = sc; bx = nx; by = ny; }
         }
     }
     reinterpret_cast<int2*>(p1_out)[t] = make_int2(bx, by);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Tiled kernel.
+// ------------------------------------------------------------------------------------------------
+constexpr int kTileX = 32, kTileY = 16, kQ = 4;      // queries per CTA: 32 x 16, 4 per thread (in y)
+constexpr int kWinX = 40, kWinY = 24;                // staged candidate window (pixels)
+constexpr int kMaxTiledRadius = 3;                   // 32 + 2*3 <= 40, 16 + 2*3 <= 24 (2 px slack)
+
+template <int D4>
+struct TiledCfg {
+    static constexpr int pitch4 = D4 + 1;                               // float4 per pixel (+16 B pad)
+    static constexpr size_t smem_bytes = (size_t)kWinX * kWinY * pitch4 * 16;
+};
+
+template <int D4, typename PT>
+__global__ void __launch_bounds__(kRefineThreads, 2)
+refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21,
+                    const PT* __restrict__ p1, int32_t* __restrict__ p1_out, int H, int W,
+                    int radius) {
+    extern __shared__ float4 tile[];  // [kWinY][kWinX][pitch4]
+    __shared__ int s_min[2], s_max[2], s_fit;
+    constexpr int P4 = TiledCfg<D4>::pitch4;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b = blockIdx.z;
+    const int qx = blockIdx.x * kTileX + lane;
+    const int qy0 = blockIdx.y * kTileY + warp * kQ;
+    const size_t N = (size_t)H * W;
+    const float4* __restrict__ img = reinterpret_cast<const float4*>(D11) + (size_t)b * N * D4;
+
+    if (threadIdx.x == 0) {
+        s_min[0] = s_min[1] = INT_MAX;
+        s_max[0] = s_max[1] = INT_MIN;
+        s_fit = 0;
+    }
+    // centres + query descriptors (issued early; consumed after the staging barrier)
+    int cx[kQ], cy[kQ];
+    bool ok[kQ];
+    float4 q[kQ][D4];
+    int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
+#pragma unroll
+    for (int k = 0; k < kQ; ++k) {
+        const int qy = qy0 + k;
+        ok[k] = (qx < W) && (qy < H);
+        cx[k] = cy[k] = 0;
+        if (ok[k]) {
+            const size_t t = (size_t)b * N + (size_t)qy * W + qx;
+            const int2 c = load_center(p1, (long long)t);
+            cx[k] = c.x; cy[k] = c.y;
+            const float4* __restrict__ qp = reinterpret_cast<const float4*>(D21) + t * D4;
+#pragma unroll
+            for (int j = 0; j < D4; ++j) q[k][j] = __ldg(qp + j);
+            mnx = min(mnx, c.x); mxx = max(mxx, c.x);
+            mny = min(mny, c.y); mxy = max(mxy, c.y);
+        }
+    }
+    __syncthreads();
+    mnx = __reduce_min_sync(0xffffffffu, mnx); mny = __reduce_min_sync(0xffffffffu, mny);
+    mxx = __reduce_max_sync(0xffffffffu, mxx); mxy = __reduce_max_sync(0xffffffffu, mxy);
+    if (lane == 0) {
+        atomicMin(&s_min[0], mnx); atomicMin(&s_min[1], mny);
+        atomicMax(&s_max[0], mxx); atomicMax(&s_max[1], mxy);
+    }
+    __syncthreads();
+    if (s_min[0] == INT_MAX) return;  // tile entirely outside the image
+    // window origin: centre the slack around the bounding box of the centres
+    const int ext_x = s_max[0] - s_min[0] + 1 + 2 * radius, ext_y = s_max[1] - s_min[1] + 1 + 2 * radius;
+    const int wx0 = s_min[0] - radius - max((kWinX - ext_x) / 2, 0);
+    const int wy0 = s_min[1] - radius - max((kWinY - ext_y) / 2, 0);
+    bool fit[kQ];
+    int nfit = 0, nok = 0;
+#pragma unroll
+    for (int k = 0; k < kQ; ++k) {
+        fit[k] = ok[k] && (cx[k] - radius >= wx0) && (cx[k] + radius < wx0 + kWinX) &&
+                 (cy[k] - radius >= wy0) && (cy[k] + radius < wy0 + kWinY);
+        nfit += fit[k];
+        nok += ok[k];
+    }
+    {
+        const int v = __reduce_add_sync(0xffffffffu, nfit * 1024 + nok);  // <= 128 each: no overflow
+        if (lane == 0) atomicAdd(&s_fit, v);
+    }
+    __syncthreads();
+    const bool use_tile = (s_fit >> 10) * 4 >= (s_fit & 1023);  // >= 25 % of the queries fit
+    if (use_tile) {
+        // cooperative staging: consecutive threads -> consecutive float4 of a window row
+        for (int i = threadIdx.x; i < kWinX * kWinY * D4; i += kRefineThreads) {
+            const int pix = i / D4, ch = i - pix * D4;
+            const int wy = pix / kWinX, wx = pix - wy * kWinX;
+            const int gx = wx0 + wx, gy = wy0 + wy;
+            if (gx >= 0 && gx < W && gy >= 0 && gy < H)
+                tile[pix * P4 + ch] = __ldg(img + ((size_t)gy * W + gx) * D4 + ch);
+        }
+    }
+    __syncthreads();
+
+    float best[kQ];
+    int bx[kQ], by[kQ];
+#pragma unroll
+    for (int k = 0; k < kQ; ++k) { best[k] = -INFINITY; bx[k] = cx[k]; by[k] = cy[k]; }
+
+    if (use_tile) {
+        int X0 = INT_MAX, X1 = INT_MIN, Y0 = INT_MAX, Y1 = INT_MIN;
+#pragma unroll
+        for (int k = 0; k < kQ; ++k)
+            if (fit[k]) {
+                X0 = min(X0, cx[k] - radius); X1 = max(X1, cx[k] + radius);
+                Y0 = min(Y0, cy[k] - radius); Y1 = max(Y1, cy[k] + radius);
+            }
+        X0 = max(X0, 0); X1 = min(X1, W - 1);
+        Y0 = max(Y0, 0); Y1 = min(Y1, H - 1);
+        for (int yy = Y0; yy <= Y1; ++yy) {
+            unsigned kmask = 0;
+#pragma unroll
+            for (int k = 0; k < kQ; ++k)
+                if (fit[k] && abs(yy - cy[k]) <= radius) kmask |= 1u << k;
+            if (!kmask) continue;
+            const float4* __restrict__ row = tile + ((yy - wy0) * kWinX - wx0) * P4;
+            for (int xx = X0; xx <= X1; ++xx) {
+                float4 c[D4];
+#pragma unroll
+                for (int j = 0; j < D4; ++j) c[j] = row[xx * P4 + j];
+#pragma unroll
+                for (int k = 0; k < kQ; ++k) {
+                    if ((kmask >> k) & 1u) {
+                        Acc4 a;
+#pragma unroll
+                        for (int j = 0; j < D4; ++j) a.fma4(q[k][j], c[j]);
+                        const float sc = a.sum();
+                        if (abs(xx - cx[k]) <= radius && sc > best[k]) {
+                            best[k] = sc; bx[k] = xx; by[k] = yy;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    // queries whose window is not covered by the staged tile: generic global path
+#pragma unroll
+    for (int k = 0; k < kQ; ++k) {
+        if (ok[k] && !(use_tile && fit[k])) scan_global<D4>(img, q[k], cx[k], cy[k], radius, H, W, bx[k], by[k]);
+        if (ok[k]) {
+            const size_t t = (size_t)b * N + (size_t)(qy0 + k) * W + qx;
+            reinterpret_cast<int2*>(p1_out)[t] = make_int2(bx[k], by[k]);
+        }
+    }
 }
 
 template <typename PT>
@@ -94,8 +268,16 @@ int refine_dispatch(const float* D11, const float* D21, const PT* p1, int32_t* p
                     int H, int W, int D, int N, int radius, cudaStream_t st) {
     const long long total = (long long)B * N;
     if (total == 0) return M3S_OK;
-    const unsigned grid = (unsigned)((total + kRefineThreads - 1) / kRefineThreads);
     const bool aligned = ((reinterpret_cast<uintptr_t>(D11) | reinterpret_cast<uintptr_t>(D21)) & 15) == 0;
+    if (aligned && D == 24 && N == H * W && radius >= 1 && radius <= kMaxTiledRadius && B <= 65535) {
+        constexpr size_t smem = TiledCfg<6>::smem_bytes;
+        M3S_CUDA(cudaFuncSetAttribute(refine_tiled_kernel<6, PT>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const dim3 grid((W + kTileX - 1) / kTileX, (H + kTileY - 1) / kTileY, B);
+        refine_tiled_kernel<6, PT><<<grid, kRefineThreads, smem, st>>>(D11, D21, p1, p1_out, H, W, radius);
+        return launch_ok("refine_tiled_kernel");
+    }
+    const unsigned grid = (unsigned)((total + kRefineThreads - 1) / kRefineThreads);
 #define M3S_REFINE_CASE(DD)                                                                     \
     case DD:                                                                                    \
         refine_kernel_vec<DD / 4, PT><<<grid, kRefineThreads, 0, st>>>(D11, D21, p1, p1_out, H, \

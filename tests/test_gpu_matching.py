@@ -222,3 +222,38 @@ def test_full_size_config1(K, oracle, synth):
     ok = valid[0, :, 0]
     err = np.abs(p[0][ok] - flow[ok]).max(-1)
     assert np.median(err) < 0.5 and ok.mean() > 0.9
+
+
+@pytest.mark.parametrize("hw", [(50, 70), (16, 32), (37, 129)])
+def test_refine_tiled_path(K, oracle, synth, hw):
+    """full-frame queries (N == H*W, D == 24): the shared-memory tiled kernel, coherent and
+    incoherent centres, ragged image sizes, all radii it accepts, B = 2"""
+    h, w = hw
+    rng = np.random.default_rng(h * w)
+    b, d = 2, 24
+    D11 = (rng.integers(-128, 129, (b, h, w, d)) / 64.0).astype(np.float32)
+    D21 = (rng.integers(-128, 129, (b, h * w, d)) / 64.0).astype(np.float32)
+    yy, xx = np.meshgrid(np.arange(h), np.arange(w), indexing="ij")
+    ident = np.stack([xx, yy], -1).reshape(1, h * w, 2)
+    coherent = np.repeat(ident, b, 0) + np.array([2, -1])
+    jitter = coherent + rng.integers(-1, 2, coherent.shape)
+    # a few wild outliers inside otherwise coherent tiles + centres outside the image
+    outl = jitter.copy()
+    sel = rng.random((b, h * w)) < 0.03
+    outl[sel] = np.stack([rng.integers(-5, w + 5, sel.sum()), rng.integers(-5, h + 5, sel.sum())], -1)
+    random = np.stack([rng.integers(-4, w + 4, (b, h * w)), rng.integers(-4, h + 4, (b, h * w))], -1)
+    for name, p1 in (("coherent", coherent), ("jitter", jitter), ("outliers", outl), ("random", random)):
+        p1 = p1.astype(np.int32)
+        for r in (1, 2, 3):
+            out = K.refine_matches(D11, D21, p1, r, 0)
+            ref = oracle.refine_matches(D11, D21, p1, r, 0)
+            assert np.array_equal(out, ref), (name, r, int((out != ref).any(-1).sum()))
+    # float positions (truncation fused into the load) through the tiled kernel
+    pf = (jitter + rng.random(jitter.shape) * 0.99).astype(np.float32)
+    out = K.refine_matches(D11, D21, pf, 3, 0)
+    ref = oracle.refine_matches(D11, D21, pf.astype(np.int32), 3, 0)
+    assert np.array_equal(out, ref)
+    # ties everywhere: first candidate in scan order must win in the tiled kernel too
+    out = K.refine_matches(np.ones_like(D11), D21, jitter.astype(np.int32), 3, 0)
+    ref = oracle.refine_matches(np.ones_like(D11), D21, jitter.astype(np.int32), 3, 0)
+    assert np.array_equal(out, ref)
