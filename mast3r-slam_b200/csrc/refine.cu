@@ -7,7 +7,7 @@
 //
 // Scores are fp32 sums over D products.  The reference's np.dot is BLAS sdot whose summation order
 // is unspecified; every kernel here uses ONE canonical order -- four component-wise FMA chains over
-// the float4 chunks, combined as (x + y) + (z + w) -- so all code paths agree bit for bit with each
+// the float4 chunks, combined as (x + z) + (y + w) -- so all code paths agree bit for bit with each
 // other; for descriptors on a dyadic grid every order is exact and the argmax equals the
 // reference's unconditionally.
 //
@@ -43,7 +43,7 @@ struct Acc4 {
         xy = __ffma2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y), xy);
         zw = __ffma2_rn(make_float2(a.z, a.w), make_float2(b.z, b.w), zw);
     }
-    __device__ __forceinline__ float sum() const { return (xy.x + xy.y) + (zw.x + zw.y); }
+    __device__ __forceinline__ float sum() const { return (xy.x + zw.x) + (xy.y + zw.y); }
 };
 
 // generic per-query scan from global memory (canonical summation order)
@@ -110,7 +110,7 @@ refine_kernel_generic(const float* __restrict__ D11, const float* __restrict__ D
             const float* __restrict__ cd = img + ((size_t)ny * W + nx) * D;
             float a[4] = {0.f, 0.f, 0.f, 0.f};
             for (int k = 0; k < D; ++k) a[k & 3] = fmaf(__ldg(qp + k), __ldg(cd + k), a[k & 3]);
-            const float sc = (a[0] + a[1]) + (a[2] + a[3]);
+            const float sc = (a[0] + a[2]) + (a[1] + a[3]);
             if (sc > best) { best = sc; bx = nx; by = ny; }
         }
     }
@@ -129,6 +129,44 @@ struct TiledCfg {
     static constexpr int pitch4 = D4 + 1;                               // float4 per pixel (+16 B pad)
     static constexpr size_t smem_bytes = (size_t)kWinX * kWinY * pitch4 * 16;
 };
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
+}
+
+// One window row for the queries selected by the compile-time mask KMASK: straight-line code, no
+// per-candidate branches.  Candidate descriptor: D4 conflict-free LDS.128, reused by every active
+// query from registers.  Position packed as (y << 16) | x.
+template <int D4, unsigned KMASK>
+__device__ __forceinline__ void row_scan(const float4* __restrict__ row, int X0, int X1, int yy,
+                                         const float4 (&q)[kQ][D4], const int (&xlo)[kQ],
+                                         unsigned span, float (&best)[kQ], int (&bpos)[kQ]) {
+    constexpr int P4 = TiledCfg<D4>::pitch4;
+    const int ybits = yy << 16;
+#pragma unroll 2
+    for (int xx = X0; xx <= X1; ++xx) {
+        float4 c[D4];
+#pragma unroll
+        for (int j = 0; j < D4; ++j) c[j] = row[xx * P4 + j];
+#pragma unroll
+        for (int k = 0; k < kQ; ++k) {
+            if ((KMASK >> k) & 1u) {
+                Acc4 a;
+#pragma unroll
+                for (int j = 0; j < D4; ++j) a.fma4(q[k][j], c[j]);
+                const float sc = a.sum();
+                if ((unsigned)(xx - xlo[k]) <= span && sc > best[k]) {
+                    best[k] = sc;
+                    bpos[k] = ybits | xx;
+                }
+            }
+        }
+    }
+}
 
 template <int D4, typename PT>
 __global__ void __launch_bounds__(kRefineThreads, 2)
@@ -150,10 +188,9 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
         s_max[0] = s_max[1] = INT_MIN;
         s_fit = 0;
     }
-    // centres + query descriptors (issued early; consumed after the staging barrier)
+    // centres first (they place the window); query descriptors are fetched while the tile streams in
     int cx[kQ], cy[kQ];
     bool ok[kQ];
-    float4 q[kQ][D4];
     int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
 #pragma unroll
     for (int k = 0; k < kQ; ++k) {
@@ -161,12 +198,8 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
         ok[k] = (qx < W) && (qy < H);
         cx[k] = cy[k] = 0;
         if (ok[k]) {
-            const size_t t = (size_t)b * N + (size_t)qy * W + qx;
-            const int2 c = load_center(p1, (long long)t);
+            const int2 c = load_center(p1, (long long)((size_t)b * N + (size_t)qy * W + qx));
             cx[k] = c.x; cy[k] = c.y;
-            const float4* __restrict__ qp = reinterpret_cast<const float4*>(D21) + t * D4;
-#pragma unroll
-            for (int j = 0; j < D4; ++j) q[k][j] = __ldg(qp + j);
             mnx = min(mnx, c.x); mxx = max(mxx, c.x);
             mny = min(mny, c.y); mxy = max(mxy, c.y);
         }
@@ -200,66 +233,88 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
     __syncthreads();
     const bool use_tile = (s_fit >> 10) * 4 >= (s_fit & 1023);  // >= 25 % of the queries fit
     if (use_tile) {
-        // cooperative staging: consecutive threads -> consecutive float4 of a window row
-        for (int i = threadIdx.x; i < kWinX * kWinY * D4; i += kRefineThreads) {
-            const int pix = i / D4, ch = i - pix * D4;
-            const int wy = pix / kWinX, wx = pix - wy * kWinX;
-            const int gx = wx0 + wx, gy = wy0 + wy;
-            if (gx >= 0 && gx < W && gy >= 0 && gy < H)
-                tile[pix * P4 + ch] = __ldg(img + ((size_t)gy * W + gx) * D4 + ch);
+        // asynchronous staging (LDGSTS, no register round trip): a window row is kWinX * D4
+        // consecutive float4 in global memory; thread t copies float4 t and t + 128 of every row.
+        constexpr int ROW4 = kWinX * D4;  // 240
+        const int f0 = threadIdx.x, f1 = threadIdx.x + kRefineThreads;
+        const int px0 = f0 / D4, px1 = f1 / D4;
+        const bool in0 = (wx0 + px0 >= 0) && (wx0 + px0 < W);
+        const bool in1 = (f1 < ROW4) && (wx0 + px1 >= 0) && (wx0 + px1 < W);
+        const int s0 = px0 * P4 + (f0 - px0 * D4), s1 = px1 * P4 + (f1 - px1 * D4);
+#pragma unroll 4
+        for (int wy = 0; wy < kWinY; ++wy) {
+            const int gy = wy0 + wy;
+            if (gy < 0 || gy >= H) continue;
+            const float4* __restrict__ src = img + ((size_t)gy * W + wx0) * D4;  // may point before the row start; only in-image elements are touched
+            float4* dst = tile + wy * kWinX * P4;
+            if (in0) cp_async16(dst + s0, src + f0);
+            if (in1) cp_async16(dst + s1, src + f1);
         }
     }
+    float4 q[kQ][D4];
+#pragma unroll
+    for (int k = 0; k < kQ; ++k) {
+        if (ok[k]) {
+            const float4* __restrict__ qp =
+                reinterpret_cast<const float4*>(D21) + ((size_t)b * N + (size_t)(qy0 + k) * W + qx) * D4;
+#pragma unroll
+            for (int j = 0; j < D4; ++j) q[k][j] = __ldg(qp + j);
+        } else {
+#pragma unroll
+            for (int j = 0; j < D4; ++j) q[k][j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    cp_async_wait_all();
     __syncthreads();
 
     float best[kQ];
-    int bx[kQ], by[kQ];
+    int bpos[kQ];
 #pragma unroll
-    for (int k = 0; k < kQ; ++k) { best[k] = -INFINITY; bx[k] = cx[k]; by[k] = cy[k]; }
+    for (int k = 0; k < kQ; ++k) { best[k] = -INFINITY; bpos[k] = -1; }
 
     if (use_tile) {
         int X0 = INT_MAX, X1 = INT_MIN, Y0 = INT_MAX, Y1 = INT_MIN;
+        int xlo[kQ];
 #pragma unroll
-        for (int k = 0; k < kQ; ++k)
+        for (int k = 0; k < kQ; ++k) {
+            xlo[k] = cx[k] - radius;
             if (fit[k]) {
                 X0 = min(X0, cx[k] - radius); X1 = max(X1, cx[k] + radius);
                 Y0 = min(Y0, cy[k] - radius); Y1 = max(Y1, cy[k] + radius);
             }
+        }
         X0 = max(X0, 0); X1 = min(X1, W - 1);
         Y0 = max(Y0, 0); Y1 = min(Y1, H - 1);
+        const unsigned span = 2u * (unsigned)radius;
         for (int yy = Y0; yy <= Y1; ++yy) {
             unsigned kmask = 0;
 #pragma unroll
             for (int k = 0; k < kQ; ++k)
-                if (fit[k] && abs(yy - cy[k]) <= radius) kmask |= 1u << k;
-            if (!kmask) continue;
+                if (fit[k] && (unsigned)(yy - (cy[k] - radius)) <= span) kmask |= 1u << k;
             const float4* __restrict__ row = tile + ((yy - wy0) * kWinX - wx0) * P4;
-            for (int xx = X0; xx <= X1; ++xx) {
-                float4 c[D4];
-#pragma unroll
-                for (int j = 0; j < D4; ++j) c[j] = row[xx * P4 + j];
-#pragma unroll
-                for (int k = 0; k < kQ; ++k) {
-                    if ((kmask >> k) & 1u) {
-                        Acc4 a;
-#pragma unroll
-                        for (int j = 0; j < D4; ++j) a.fma4(q[k][j], c[j]);
-                        const float sc = a.sum();
-                        if (abs(xx - cx[k]) <= radius && sc > best[k]) {
-                            best[k] = sc; bx[k] = xx; by[k] = yy;
-                        }
-                    }
-                }
+#define M3S_ROW(MASK) case MASK: row_scan<D4, MASK>(row, X0, X1, yy, q, xlo, span, best, bpos); break
+            switch (kmask) {
+                case 0: break;
+                M3S_ROW(1); M3S_ROW(2); M3S_ROW(3); M3S_ROW(4); M3S_ROW(5); M3S_ROW(6); M3S_ROW(7);
+                M3S_ROW(8); M3S_ROW(9); M3S_ROW(10); M3S_ROW(11); M3S_ROW(12); M3S_ROW(13);
+                M3S_ROW(14); M3S_ROW(15);
             }
+#undef M3S_ROW
         }
     }
     // queries whose window is not covered by the staged tile: generic global path
 #pragma unroll
     for (int k = 0; k < kQ; ++k) {
-        if (ok[k] && !(use_tile && fit[k])) scan_global<D4>(img, q[k], cx[k], cy[k], radius, H, W, bx[k], by[k]);
-        if (ok[k]) {
-            const size_t t = (size_t)b * N + (size_t)(qy0 + k) * W + qx;
-            reinterpret_cast<int2*>(p1_out)[t] = make_int2(bx[k], by[k]);
+        if (!ok[k]) continue;
+        int bx, by;
+        if (use_tile && fit[k]) {
+            bx = (bpos[k] < 0) ? cx[k] : (bpos[k] & 0xffff);
+            by = (bpos[k] < 0) ? cy[k] : (bpos[k] >> 16);
+        } else {
+            scan_global<D4>(img, q[k], cx[k], cy[k], radius, H, W, bx, by);
         }
+        const size_t t = (size_t)b * N + (size_t)(qy0 + k) * W + qx;
+        reinterpret_cast<int2*>(p1_out)[t] = make_int2(bx, by);
     }
 }
 
