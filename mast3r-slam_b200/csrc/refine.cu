@@ -43,7 +43,10 @@ struct Acc4 {
         xy = __ffma2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y), xy);
         zw = __ffma2_rn(make_float2(a.z, a.w), make_float2(b.z, b.w), zw);
     }
-    __device__ __forceinline__ float sum() const { return (xy.x + zw.x) + (xy.y + zw.y); }
+    __device__ __forceinline__ float sum() const {
+        const float2 t = __fadd2_rn(xy, zw);
+        return t.x + t.y;
+    }
 };
 
 // generic per-query scan from global memory (canonical summation order)
@@ -138,30 +141,35 @@ __device__ __forceinline__ void cp_async_wait_all() {
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
 }
 
-// One window row for the queries selected by the compile-time mask KMASK: straight-line code, no
-// per-candidate branches.  Candidate descriptor: D4 conflict-free LDS.128, reused by every active
-// query from registers.  Position packed as (y << 16) | x.
+// One (warp-uniform) window row for the queries selected by the compile-time mask KMASK:
+// straight-line code, no per-candidate branches.  Every lane walks NC columns of ITS OWN window
+// (lane-relative column i -> smem column min(xb + i, kWinX - 1)); a candidate descriptor is D4
+// conflict-free LDS.128 and is reused from registers by every active query.  Lanes / queries for
+// which the candidate is outside their own (2r+1)^2 window compute a dot product that the compare
+// predicate discards.  Position packed as (row << 16) | col in lane-relative window coordinates.
 template <int D4, unsigned KMASK>
-__device__ __forceinline__ void row_scan(const float4* __restrict__ row, int X0, int X1, int yy,
-                                         const float4 (&q)[kQ][D4], const int (&xlo)[kQ],
-                                         unsigned span, float (&best)[kQ], int (&bpos)[kQ]) {
+__device__ __forceinline__ void row_scan(const float4* __restrict__ row, int xb, int NC, int j,
+                                         const float4 (&q)[kQ][D4], const bool (&rowok)[kQ],
+                                         const int (&xlo)[kQ], const unsigned (&xspan)[kQ],
+                                         float (&best)[kQ], int (&bpos)[kQ]) {
     constexpr int P4 = TiledCfg<D4>::pitch4;
-    const int ybits = yy << 16;
+    const int jbits = j << 16;
 #pragma unroll 2
-    for (int xx = X0; xx <= X1; ++xx) {
+    for (int i = 0; i < NC; ++i) {
+        const float4* __restrict__ cp = row + min(xb + i, kWinX - 1) * P4;
         float4 c[D4];
 #pragma unroll
-        for (int j = 0; j < D4; ++j) c[j] = row[xx * P4 + j];
+        for (int d = 0; d < D4; ++d) c[d] = cp[d];
 #pragma unroll
         for (int k = 0; k < kQ; ++k) {
             if ((KMASK >> k) & 1u) {
                 Acc4 a;
 #pragma unroll
-                for (int j = 0; j < D4; ++j) a.fma4(q[k][j], c[j]);
+                for (int d = 0; d < D4; ++d) a.fma4(q[k][d], c[d]);
                 const float sc = a.sum();
-                if ((unsigned)(xx - xlo[k]) <= span && sc > best[k]) {
+                if (rowok[k] && (unsigned)(i - xlo[k]) <= xspan[k] && sc > best[k]) {
                     best[k] = sc;
-                    bpos[k] = ybits | xx;
+                    bpos[k] = jbits | i;
                 }
             }
         }
@@ -245,7 +253,8 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
         for (int wy = 0; wy < kWinY; ++wy) {
             const int gy = wy0 + wy;
             if (gy < 0 || gy >= H) continue;
-            const float4* __restrict__ src = img + ((size_t)gy * W + wx0) * D4;  // may point before the row start; only in-image elements are touched
+            // `src` may point before the row start when wx0 < 0; only in-image elements are touched
+            const float4* __restrict__ src = img + ((long long)gy * W + wx0) * D4;
             float4* dst = tile + wy * kWinX * P4;
             if (in0) cp_async16(dst + s0, src + f0);
             if (in1) cp_async16(dst + s1, src + f1);
@@ -258,10 +267,10 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
             const float4* __restrict__ qp =
                 reinterpret_cast<const float4*>(D21) + ((size_t)b * N + (size_t)(qy0 + k) * W + qx) * D4;
 #pragma unroll
-            for (int j = 0; j < D4; ++j) q[k][j] = __ldg(qp + j);
+            for (int d = 0; d < D4; ++d) q[k][d] = __ldg(qp + d);
         } else {
 #pragma unroll
-            for (int j = 0; j < D4; ++j) q[k][j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int d = 0; d < D4; ++d) q[k][d] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
     }
     cp_async_wait_all();
@@ -272,28 +281,44 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
 #pragma unroll
     for (int k = 0; k < kQ; ++k) { best[k] = -INFINITY; bpos[k] = -1; }
 
+    int xb = 0, yb = 0;  // this lane's window base inside the staged tile (tile-relative)
     if (use_tile) {
-        int X0 = INT_MAX, X1 = INT_MIN, Y0 = INT_MAX, Y1 = INT_MIN;
-        int xlo[kQ];
+        // lane-relative window geometry
+        int X0 = INT_MAX, Y0 = INT_MAX;
+#pragma unroll
+        for (int k = 0; k < kQ; ++k)
+            if (fit[k]) { X0 = min(X0, cx[k] - radius); Y0 = min(Y0, cy[k] - radius); }
+        if (X0 == INT_MAX) { X0 = wx0; Y0 = wy0; }  // no fitting query: walk a dummy window
+        xb = X0 - wx0;
+        yb = Y0 - wy0;
+        int nr = 0, nc = 0;
+        int ylo[kQ], xlo[kQ];
+        unsigned yspan[kQ], xspan[kQ];
 #pragma unroll
         for (int k = 0; k < kQ; ++k) {
-            xlo[k] = cx[k] - radius;
-            if (fit[k]) {
-                X0 = min(X0, cx[k] - radius); X1 = max(X1, cx[k] + radius);
-                Y0 = min(Y0, cy[k] - radius); Y1 = max(Y1, cy[k] + radius);
-            }
+            // candidate range of query k clipped to the image, in lane-relative coordinates;
+            // an empty range is encoded as lo = 0, span = UINT_MAX + 1 - ... -> use lo = 1<<20
+            const int ya = max(cy[k] - radius, 0), yz = min(cy[k] + radius, H - 1);
+            const int xa = max(cx[k] - radius, 0), xz = min(cx[k] + radius, W - 1);
+            const bool any = fit[k] && ya <= yz && xa <= xz;
+            ylo[k] = any ? ya - Y0 : (1 << 20);
+            xlo[k] = any ? xa - X0 : (1 << 20);
+            yspan[k] = any ? (unsigned)(yz - ya) : 0u;
+            xspan[k] = any ? (unsigned)(xz - xa) : 0u;
+            if (any) { nr = max(nr, yz - Y0 + 1); nc = max(nc, xz - X0 + 1); }
         }
-        X0 = max(X0, 0); X1 = min(X1, W - 1);
-        Y0 = max(Y0, 0); Y1 = min(Y1, H - 1);
-        const unsigned span = 2u * (unsigned)radius;
-        for (int yy = Y0; yy <= Y1; ++yy) {
+        const int NR = __reduce_max_sync(0xffffffffu, nr), NC = __reduce_max_sync(0xffffffffu, nc);
+        for (int j = 0; j < NR; ++j) {
+            bool rowok[kQ];
             unsigned kmask = 0;
 #pragma unroll
-            for (int k = 0; k < kQ; ++k)
-                if (fit[k] && (unsigned)(yy - (cy[k] - radius)) <= span) kmask |= 1u << k;
-            const float4* __restrict__ row = tile + ((yy - wy0) * kWinX - wx0) * P4;
-#define M3S_ROW(MASK) case MASK: row_scan<D4, MASK>(row, X0, X1, yy, q, xlo, span, best, bpos); break
-            switch (kmask) {
+            for (int k = 0; k < kQ; ++k) {
+                rowok[k] = (unsigned)(j - ylo[k]) <= yspan[k];
+                if (__any_sync(0xffffffffu, rowok[k])) kmask |= 1u << k;
+            }
+            const float4* __restrict__ row = tile + (min(yb + j, kWinY - 1) * kWinX) * P4;
+#define M3S_ROW(MASK) case MASK: row_scan<D4, MASK>(row, xb, NC, j, q, rowok, xlo, xspan, best, bpos); break
+            switch (kmask) {  // warp-uniform
                 case 0: break;
                 M3S_ROW(1); M3S_ROW(2); M3S_ROW(3); M3S_ROW(4); M3S_ROW(5); M3S_ROW(6); M3S_ROW(7);
                 M3S_ROW(8); M3S_ROW(9); M3S_ROW(10); M3S_ROW(11); M3S_ROW(12); M3S_ROW(13);
@@ -302,14 +327,14 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
 #undef M3S_ROW
         }
     }
-    // queries whose window is not covered by the staged tile: generic global path
+    // write-back; queries whose window is not covered by the staged tile take the global path
 #pragma unroll
     for (int k = 0; k < kQ; ++k) {
         if (!ok[k]) continue;
         int bx, by;
         if (use_tile && fit[k]) {
-            bx = (bpos[k] < 0) ? cx[k] : (bpos[k] & 0xffff);
-            by = (bpos[k] < 0) ? cy[k] : (bpos[k] >> 16);
+            bx = (bpos[k] < 0) ? cx[k] : (wx0 + xb + (bpos[k] & 0xffff));
+            by = (bpos[k] < 0) ? cy[k] : (wy0 + yb + (bpos[k] >> 16));
         } else {
             scan_global<D4>(img, q[k], cx[k], cy[k], radius, H, W, bx, by);
         }
