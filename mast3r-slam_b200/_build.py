@@ -32,6 +32,22 @@ def _newer(target, deps):
     return all(os.path.getmtime(d) <= t for d in deps)
 
 
+def build_variant(name: str, defines: list[str]) -> str:
+    """Development helper: build libm3s_b200_<name>.so with extra -D flags (A/B experiments;
+    select it at run time with M3S_LIB=<path>)."""
+    odir = os.path.join(OBJ_DIR, name)
+    os.makedirs(odir, exist_ok=True)
+    objs = []
+    for src, extra in SOURCES.items():
+        o = os.path.join(odir, src.replace(".cu", ".o"))
+        subprocess.check_call(["nvcc", *ARCH, *COMMON, *extra, *[f"-D{d}" for d in defines], "-c",
+                               os.path.join(CSRC, src), "-o", o])
+        objs.append(o)
+    so = os.path.join(PKG, f"libm3s_b200_{name}.so")
+    subprocess.check_call(["nvcc", *ARCH, "-shared", "-o", so, *objs, "-ccbin", "g++"])
+    return so
+
+
 def build_native(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ_DIR, exist_ok=True)
     headers = [os.path.join(CSRC, "m3s_common.cuh"), os.path.join(ROOT, "include", "m3s.h")]

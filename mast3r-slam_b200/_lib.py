@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_PKG, "libm3s_b200.so")
+# M3S_LIB: development override to A/B-test an alternative build of the same C ABI
+SO_PATH = os.environ.get("M3S_LIB") or os.path.join(_PKG, "libm3s_b200.so")
 
 GN_RAYS, GN_POINTS, GN_CALIB = 0, 1, 2
 GN_EDGE_STRIDE = 36

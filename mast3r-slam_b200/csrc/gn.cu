@@ -137,7 +137,7 @@ __device__ __forceinline__ void accumulate_point(const KernelParams& P, const Ed
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             const double ra = fabs(sqrt_w * err[c]);
-            const double w = (ra < kHuber) ? w2 : (kHuber / ra) * w2;
+            const double w = (ra < kHuber) ? w2 : (kHuber * __drcp_rn(ra)) * w2;
             int k = 0;
 #pragma unroll
             for (int a = 0; a < 7; ++a) {
@@ -160,9 +160,10 @@ __device__ __forceinline__ void accumulate_point(const KernelParams& P, const Ed
         }
         const double sqrt_w = sw, w2 = (double)__fmul_rn(sw, sw);
         const double r0 = fabs(sqrt_w * e0), r1 = fabs(sqrt_w * e1), r2 = fabs(sqrt_w * e2);
-        const double w0 = (r0 < kHuber) ? w2 : (kHuber / r0) * w2;
-        const double w1 = (r1 < kHuber) ? w2 : (kHuber / r1) * w2;
-        const double w2c = (r2 < kHuber) ? w2 : (kHuber / r2) * w2;
+        // Huber (sim3_ops.py:295-306): k / |r| via reciprocal (within 1 ulp of the division)
+        const double w0 = (r0 < kHuber) ? w2 : (kHuber * __drcp_rn(r0)) * w2;
+        const double w1 = (r1 < kHuber) ? w2 : (kHuber * __drcp_rn(r1)) * w2;
+        const double w2c = (r2 < kHuber) ? w2 : (kHuber * __drcp_rn(r2)) * w2;
         const double w0y = w0 * y, w0z = w0 * z, w1x = w1 * x, w1z = w1 * z, w2x = w2c * x,
                      w2y = w2c * y;
         const double w0x = w0 * x, w1y = w1 * y, w2z = w2c * z;
@@ -189,12 +190,13 @@ __device__ __forceinline__ void accumulate_point(const KernelParams& P, const Ed
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(kAccThreads)
+__global__ void __launch_bounds__(kAccThreads, 2)
 gn_accum_kernel(const Status* __restrict__ status, KernelParams P, const double* __restrict__ poses,
                 const EdgeMeta* __restrict__ meta, const float* __restrict__ Xs,
                 const float* __restrict__ Cs, const int32_t* __restrict__ idx,
                 const uint8_t* __restrict__ valid, const float* __restrict__ Q, long long N,
-                int edge_begin, int nchunks, long long chunk_pts, double* __restrict__ partials) {
+                int edge_begin, int nchunks, long long chunk_pts, int vec_ok,
+                double* __restrict__ partials) {
     if (status->stopped | status->failed) return;
     constexpr int NA = AccCount<MODE>::value;
     const int e = edge_begin + blockIdx.x / nchunks;
@@ -241,16 +243,58 @@ gn_accum_kernel(const Status* __restrict__ status, KernelParams P, const double*
 
     const long long n0 = (long long)chunk * chunk_pts;
     const long long n1 = min(N, n0 + chunk_pts);
-    for (long long n = n0 + threadIdx.x; n < n1; n += kAccThreads) {
-        if (!__ldg(ve + n)) continue;
-        const float qc = __ldg(Qe + n);
-        long long m = __ldg(ide + n);
-        if (m < 0) m += N;  // numpy negative indexing (gauss_newton.py:125)
-        if (m < 0 || m >= N) continue;
-        if (!(qc > P.q_th) || !(__ldg(Cj + n) > P.c_th) || !(__ldg(Ci + m) > P.c_th)) continue;
-        accumulate_point<MODE>(P, ec, __ldg(Xj + 3 * n), __ldg(Xj + 3 * n + 1), __ldg(Xj + 3 * n + 2),
-                               __ldg(Xi + 3 * m), __ldg(Xi + 3 * m + 1), __ldg(Xi + 3 * m + 2), qc,
-                               acc);
+    if (vec_ok) {
+        // Vector path (N % 4 == 0, chunk_pts % 4 == 0): each thread takes 4 consecutive points per
+        // trip.  All streaming loads (valid uchar4, Q / Cj float4, idx int4, Xj 3 x float4) are
+        // issued together, then the 4 gathers of (Ci, Xi) with clamped indices, and only then the
+        // arithmetic: 4x the memory-level parallelism of a point-at-a-time loop and no load sits
+        // behind a data-dependent branch (first version: 66 % of stall samples were long-scoreboard).
+        const uchar4* __restrict__ v4p = reinterpret_cast<const uchar4*>(ve);
+        const float4* __restrict__ q4p = reinterpret_cast<const float4*>(Qe);
+        const int4* __restrict__ i4p = reinterpret_cast<const int4*>(ide);
+        const float4* __restrict__ c4p = reinterpret_cast<const float4*>(Cj);
+        const float4* __restrict__ x4p = reinterpret_cast<const float4*>(Xj);
+        for (long long g = (n0 >> 2) + threadIdx.x; g < (n1 >> 2); g += kAccThreads) {
+            const uchar4 v4 = __ldg(v4p + g);
+            const float4 q4 = __ldg(q4p + g);
+            const int4 i4 = __ldg(i4p + g);
+            const float4 c4 = __ldg(c4p + g);
+            const float4 xa = __ldg(x4p + 3 * g), xb = __ldg(x4p + 3 * g + 1), xc = __ldg(x4p + 3 * g + 2);
+            const unsigned char vv[4] = {v4.x, v4.y, v4.z, v4.w};
+            const float qq[4] = {q4.x, q4.y, q4.z, q4.w};
+            const int ii4[4] = {i4.x, i4.y, i4.z, i4.w};
+            const float cc[4] = {c4.x, c4.y, c4.z, c4.w};
+            const float xj[4][3] = {{xa.x, xa.y, xa.z}, {xa.w, xb.x, xb.y}, {xb.z, xb.w, xc.x}, {xc.y, xc.z, xc.w}};
+            bool okp[4];
+            float ci[4], xi[4][3];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                long long m = ii4[u];
+                if (m < 0) m += N;  // numpy negative indexing (gauss_newton.py:125)
+                okp[u] = vv[u] && (m >= 0) && (m < N) && (qq[u] > P.q_th) && (cc[u] > P.c_th);
+                m = okp[u] ? m : 0;  // clamped gather: no branch in front of the load
+                ci[u] = __ldg(Ci + m);
+                xi[u][0] = __ldg(Xi + 3 * m); xi[u][1] = __ldg(Xi + 3 * m + 1); xi[u][2] = __ldg(Xi + 3 * m + 2);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (okp[u] && (ci[u] > P.c_th))
+                    accumulate_point<MODE>(P, ec, xj[u][0], xj[u][1], xj[u][2], xi[u][0], xi[u][1],
+                                           xi[u][2], qq[u], acc);
+            }
+        }
+    } else {
+        for (long long n = n0 + threadIdx.x; n < n1; n += kAccThreads) {
+            if (!__ldg(ve + n)) continue;
+            const float qc = __ldg(Qe + n);
+            long long m = __ldg(ide + n);
+            if (m < 0) m += N;  // numpy negative indexing (gauss_newton.py:125)
+            if (m < 0 || m >= N) continue;
+            if (!(qc > P.q_th) || !(__ldg(Cj + n) > P.c_th) || !(__ldg(Ci + m) > P.c_th)) continue;
+            accumulate_point<MODE>(P, ec, __ldg(Xj + 3 * n), __ldg(Xj + 3 * n + 1), __ldg(Xj + 3 * n + 2),
+                                   __ldg(Xi + 3 * m), __ldg(Xi + 3 * m + 1), __ldg(Xi + 3 * m + 2), qc,
+                                   acc);
+        }
     }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -422,9 +466,34 @@ __global__ void gn_pad_diag_kernel(const Status* __restrict__ status, double* __
 // ------------------------------------------------------------------------------------------------
 constexpr int kTrsmRows = 128;
 
+// 32x32 Cholesky in shared memory by the whole CTA (128 threads): per column one sqrt/reciprocal,
+// one column scale, one rank-1 update of the trailing block; 3 barriers per column.
+__device__ __forceinline__ void chol32_smem(double (*D)[kNB + 1], double* dinv, int* bad) {
+    const int tid = threadIdx.x;
+    const int tc = tid & 31, tr = tid >> 5;
+    for (int j = 0; j < kNB; ++j) {
+        if (tid == 0) {
+            double djj = D[j][j];
+            if (!((djj > 0.0) && (djj < 1e300))) { *bad = 1; djj = 1.0; }
+            const double ljj = sqrt(djj);
+            D[j][j] = ljj;
+            dinv[j] = 1.0 / ljj;
+        }
+        __syncthreads();
+        if (tid > j && tid < kNB) D[tid][j] *= dinv[j];
+        __syncthreads();
+        if (tc > j)
+            for (int r = j + 1 + tr; r < kNB; r += kTrsmRows / 32)
+                if (tc <= r) D[r][tc] -= D[r][j] * D[tc][j];
+        __syncthreads();
+    }
+}
+
+// grid = row tiles of the panel below the diagonal block (incl. the rhs row) + 1 extra CTA that
+// inverts the diagonal factor (used by the back-substitution).
 __global__ void __launch_bounds__(kTrsmRows)
 chol_panel_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* __restrict__ Ldiag,
-                  int np, int k0) {
+                  double* __restrict__ Linv, int np, int k0) {
     if (status->stopped | status->failed | status->chol_fail) return;
     __shared__ double D[kNB][kNB + 1];
     __shared__ double dinv[kNB];
@@ -436,34 +505,30 @@ chol_panel_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* 
     }
     if (tid == 0) bad = 0;
     __syncthreads();
-    if (tid < 32) {
-        // warp-level unblocked Cholesky: lane = row
-        const int r = tid;
-        for (int j = 0; j < kNB; ++j) {
-            double djj = D[j][j];
-            const bool ok = (djj > 0.0) && (djj == djj) && (djj < 1e300);
-            if (!ok) { if (r == 0) bad = 1; djj = 1.0; }
-            const double ljj = sqrt(djj);
-            const double inv = 1.0 / ljj;
-            __syncwarp();
-            if (r == j) { D[j][j] = ljj; dinv[j] = inv; }
-            double lrj = 0.0;
-            if (r > j) { lrj = D[r][j] * inv; D[r][j] = lrj; }
-            __syncwarp();
-            // trailing update of row r: D[r][c] -= L[r][j] * L[c][j] for j < c <= r
-            if (r > j)
-                for (int c = j + 1; c <= r; ++c) D[r][c] -= lrj * D[c][j];
-            __syncwarp();
-        }
-    }
-    __syncthreads();
+    chol32_smem(D, dinv, &bad);
     if (bad) {
         if (blockIdx.x == 0 && tid == 0) status->chol_fail = 1;
         return;
     }
-    if (blockIdx.x == 0) {
+    if (blockIdx.x == gridDim.x - 1) {
+        // extra CTA: store L11 and its inverse.  Lane c of warp 0 solves L x = e_c (column c of
+        // L^-1) by forward substitution with the column in registers.
         double* Ld = Ldiag + (size_t)(k0 / kNB) * kNB * kNB;
         for (int i = tid; i < kNB * kNB; i += blockDim.x) Ld[i] = D[i / kNB][i % kNB];
+        if (tid < 32) {
+            double x[kNB];
+#pragma unroll
+            for (int r = 0; r < kNB; ++r) {
+                double sacc = (r == tid) ? 1.0 : 0.0;
+#pragma unroll
+                for (int k = 0; k < r; ++k) sacc -= D[r][k] * x[k];
+                x[r] = sacc * dinv[r];
+            }
+            double* Li = Linv + (size_t)(k0 / kNB) * kNB * kNB;
+#pragma unroll
+            for (int r = 0; r < kNB; ++r) Li[r * kNB + tid] = x[r];  // row r, column tid
+        }
+        return;
     }
     // rows below the diagonal block, including the rhs row np
     const int row = k0 + kNB + blockIdx.x * kTrsmRows + tid;
@@ -578,12 +643,14 @@ constexpr int kSolveThreads = 1024;
 
 __global__ void __launch_bounds__(kSolveThreads)
 gn_backsolve_update_kernel(Status* __restrict__ status, const double* __restrict__ Hm,
-                           const double* __restrict__ Ldiag, int np, int dim, int num_free,
+                           const double* __restrict__ Linv, int np, int dim, int num_free,
                            const int* __restrict__ free_kf, double delta_thresh,
                            double* __restrict__ dx_out, double* __restrict__ poses) {
     if (status->stopped | status->failed) return;
     extern __shared__ double ysh[];  // [np]
     __shared__ double red[kSolveThreads / 32];
+    __shared__ double Lsh[kNB * kNB];
+    __shared__ double xsh[kNB];
     __shared__ int decision;  // 0 apply, 1 stop, 2 fail
     const int tid = threadIdx.x;
     if (status->chol_fail) {
@@ -594,28 +661,26 @@ gn_backsolve_update_kernel(Status* __restrict__ status, const double* __restrict
     __syncthreads();
     const int nblk = np / kNB;
     for (int b = nblk - 1; b >= 0; --b) {
+        // x_b = L_bb^-T y_b = sum_r Linv[r][i] y_r: Linv block staged by all 1024 threads, then
+        // one 32-term dot product per lane of warp 0
+        Lsh[tid] = Linv[(size_t)b * kNB * kNB + tid];
+        __syncthreads();
         if (tid < 32) {
-            // solve L_bb^T x = y_b : lane i owns y_i; columns of L_bb^T are rows of L_bb
-            const double* Ld = Ldiag + (size_t)b * kNB * kNB;
-            double yi = ysh[b * kNB + tid];
-            for (int j = kNB - 1; j >= 0; --j) {
-                double xj = 0.0;
-                if (tid == j) xj = yi / Ld[j * kNB + j];
-                xj = __shfl_sync(0xffffffffu, xj, j);
-                if (tid == j) yi = xj;
-                else if (tid < j) yi -= Ld[j * kNB + tid] * xj;
-            }
-            ysh[b * kNB + tid] = yi;
+            double acc = 0.0;
+#pragma unroll
+            for (int r = 0; r < kNB; ++r) acc += Lsh[r * kNB + tid] * ysh[b * kNB + r];
+            xsh[tid] = acc;
         }
         __syncthreads();
+        if (tid < 32) ysh[b * kNB + tid] = xsh[tid];
         // y_c -= sum_{r in block b} L[r][c] x_r  for all columns c left of the block
         const int ncol = b * kNB;
         for (int c = tid; c < ncol; c += blockDim.x) {
-            double s = ysh[c];
+            double sacc = ysh[c];
             const double* Lr = Hm + (size_t)(b * kNB) * np + c;
 #pragma unroll 8
-            for (int r = 0; r < kNB; ++r) s -= Lr[(size_t)r * np] * ysh[b * kNB + r];
-            ysh[c] = s;
+            for (int r = 0; r < kNB; ++r) sacc -= Lr[(size_t)r * np] * xsh[r];
+            ysh[c] = sacc;
         }
         __syncthreads();
     }
@@ -692,7 +757,8 @@ struct m3s_gn_plan {
     int* list_sign = nullptr;
     int* free_kf = nullptr;         // [F]
     double* Hm = nullptr;           // [np + 1, np]
-    double* Ldiag = nullptr;        // [np / 32, 32, 32]
+    double* Ldiag = nullptr;        // [np / 32, 32, 32] diagonal factor blocks
+    double* Linv = nullptr;         // [np / 32, 32, 32] their inverses
     double* g = nullptr;            // [dim]
     double* dx = nullptr;           // [dim]
     Status* status = nullptr;
@@ -702,7 +768,7 @@ static void plan_free(m3s_gn_plan* p) {
     if (!p) return;
     cudaFree(p->poses); cudaFree(p->meta); cudaFree(p->partials); cudaFree(p->edge_blocks);
     cudaFree(p->blocks); cudaFree(p->list_edge); cudaFree(p->list_sign); cudaFree(p->free_kf);
-    cudaFree(p->Hm); cudaFree(p->Ldiag); cudaFree(p->g); cudaFree(p->dx); cudaFree(p->status);
+    cudaFree(p->Hm); cudaFree(p->Ldiag); cudaFree(p->Linv); cudaFree(p->g); cudaFree(p->dx); cudaFree(p->status);
     delete p;
 }
 
@@ -825,6 +891,7 @@ M3S_API m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii, const int32_t* jj, in
     const size_t hm = (size_t)(p->np + 1) * std::max(p->np, 1);
     ok = ok && cudaMalloc((void**)&p->Hm, sizeof(double) * hm) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&p->Ldiag, sizeof(double) * kNB * std::max(p->np, kNB)) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&p->Linv, sizeof(double) * kNB * std::max(p->np, kNB)) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&p->g, sizeof(double) * std::max(p->dim, 1)) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&p->dx, sizeof(double) * std::max(p->dim, 1)) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&p->status, sizeof(Status)) == cudaSuccess;
@@ -902,11 +969,15 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
     const int ne = edge_end - edge_begin;
     if (ne > 0 && plan->N > 0) {
         const unsigned grid = (unsigned)((long long)ne * plan->nchunks);
+        const uintptr_t al = reinterpret_cast<uintptr_t>(Xs) | reinterpret_cast<uintptr_t>(Cs) |
+                             reinterpret_cast<uintptr_t>(idx) | reinterpret_cast<uintptr_t>(Q);
+        const int vec_ok = ((plan->N & 3) == 0) && ((al & 15) == 0) &&
+                           ((reinterpret_cast<uintptr_t>(valid) & 3) == 0);
 #define M3S_ACC(MODE)                                                                           \
     gn_accum_kernel<MODE><<<grid, kAccThreads, 0, st>>>(plan->status, P, plan->poses, plan->meta, \
                                                         Xs, Cs, idx, valid, Q, plan->N,          \
                                                         edge_begin, plan->nchunks,               \
-                                                        plan->chunk_pts, plan->partials)
+                                                        plan->chunk_pts, vec_ok, plan->partials)
         if (gp->mode == M3S_GN_RAYS) M3S_ACC(M3S_GN_RAYS);
         else if (gp->mode == M3S_GN_POINTS) M3S_ACC(M3S_GN_POINTS);
         else M3S_ACC(M3S_GN_CALIB);
@@ -945,8 +1016,8 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
     const int np = plan->np;
     for (int k0 = 0; k0 < np; k0 += kNB) {
         const int rows_below = np + 1 - (k0 + kNB);  // incl. rhs row
-        const int grid = std::max(1, (rows_below + kTrsmRows - 1) / kTrsmRows);
-        chol_panel_kernel<<<grid, kTrsmRows, 0, st>>>(plan->status, plan->Hm, plan->Ldiag, np, k0);
+        const int grid = (rows_below + kTrsmRows - 1) / kTrsmRows + 1;  // + the inversion CTA
+        chol_panel_kernel<<<grid, kTrsmRows, 0, st>>>(plan->status, plan->Hm, plan->Ldiag, plan->Linv, np, k0);
         if (int rc = launch_ok("chol_panel_kernel")) return rc;
         const int trailing = np - (k0 + kNB);
         if (rows_below > 0 && trailing >= 0) {
@@ -963,7 +1034,7 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
         M3S_CUDA(cudaFuncSetAttribute(gn_backsolve_update_kernel,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
     }
-    gn_backsolve_update_kernel<<<1, kSolveThreads, sh, st>>>(plan->status, plan->Hm, plan->Ldiag, np,
+    gn_backsolve_update_kernel<<<1, kSolveThreads, sh, st>>>(plan->status, plan->Hm, plan->Linv, np,
                                                             plan->dim, plan->F, plan->free_kf,
                                                             gp->delta_thresh, plan->dx, plan->poses);
     return launch_ok("gn_backsolve_update_kernel");

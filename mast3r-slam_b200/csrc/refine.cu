@@ -40,8 +40,13 @@ struct Acc4 {
     float2 xy, zw;
     __device__ __forceinline__ Acc4() : xy(make_float2(0.f, 0.f)), zw(make_float2(0.f, 0.f)) {}
     __device__ __forceinline__ void fma4(const float4& a, const float4& b) {
+#ifdef M3S_REFINE_SCALAR_FMA  // A/B experiment: same arithmetic with four scalar FFMA
+        xy.x = fmaf(a.x, b.x, xy.x); xy.y = fmaf(a.y, b.y, xy.y);
+        zw.x = fmaf(a.z, b.z, zw.x); zw.y = fmaf(a.w, b.w, zw.y);
+#else
         xy = __ffma2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y), xy);
         zw = __ffma2_rn(make_float2(a.z, a.w), make_float2(b.z, b.w), zw);
+#endif
     }
     __device__ __forceinline__ float sum() const {
         const float2 t = __fadd2_rn(xy, zw);
@@ -148,31 +153,53 @@ __device__ __forceinline__ void cp_async_wait_all() {
 // which the candidate is outside their own (2r+1)^2 window compute a dot product that the compare
 // predicate discards.  Position packed as (row << 16) | col in lane-relative window coordinates.
 template <int D4, unsigned KMASK>
+__device__ __forceinline__ void cand_eval(const float4 (&c)[D4], int i, int jbits,
+                                          const float4 (&q)[kQ][D4], const bool (&rowok)[kQ],
+                                          const int (&xlo)[kQ], const unsigned (&xspan)[kQ],
+                                          float (&best)[kQ], int (&bpos)[kQ]) {
+    Acc4 a[kQ];
+    // chunk-outer / query-inner: 2 x popcount(KMASK) independent FFMA2 chains interleaved
+#pragma unroll
+    for (int d = 0; d < D4; ++d)
+#pragma unroll
+        for (int k = 0; k < kQ; ++k)
+            if ((KMASK >> k) & 1u) a[k].fma4(q[k][d], c[d]);
+    const int pos = jbits | i;
+#pragma unroll
+    for (int k = 0; k < kQ; ++k) {
+        if ((KMASK >> k) & 1u) {
+            const float sc = a[k].sum();
+            // bitwise & (no short-circuit): keeps this a select, not a branch
+            const bool take = rowok[k] & ((unsigned)(i - xlo[k]) <= xspan[k]) & (sc > best[k]);
+            best[k] = take ? sc : best[k];
+            bpos[k] = take ? pos : bpos[k];
+        }
+    }
+}
+
+template <int D4>
+__device__ __forceinline__ void cand_load(float4 (&c)[D4], const float4* __restrict__ row, int col) {
+    constexpr int P4 = TiledCfg<D4>::pitch4;
+    const float4* __restrict__ cp = row + min(col, kWinX - 1) * P4;
+#pragma unroll
+    for (int d = 0; d < D4; ++d) c[d] = cp[d];
+}
+
+template <int D4, unsigned KMASK>
 __device__ __forceinline__ void row_scan(const float4* __restrict__ row, int xb, int NC, int j,
                                          const float4 (&q)[kQ][D4], const bool (&rowok)[kQ],
                                          const int (&xlo)[kQ], const unsigned (&xspan)[kQ],
                                          float (&best)[kQ], int (&bpos)[kQ]) {
-    constexpr int P4 = TiledCfg<D4>::pitch4;
     const int jbits = j << 16;
-#pragma unroll 2
-    for (int i = 0; i < NC; ++i) {
-        const float4* __restrict__ cp = row + min(xb + i, kWinX - 1) * P4;
-        float4 c[D4];
-#pragma unroll
-        for (int d = 0; d < D4; ++d) c[d] = cp[d];
-#pragma unroll
-        for (int k = 0; k < kQ; ++k) {
-            if ((KMASK >> k) & 1u) {
-                Acc4 a;
-#pragma unroll
-                for (int d = 0; d < D4; ++d) a.fma4(q[k][d], c[d]);
-                const float sc = a.sum();
-                if (rowok[k] && (unsigned)(i - xlo[k]) <= xspan[k] && sc > best[k]) {
-                    best[k] = sc;
-                    bpos[k] = jbits | i;
-                }
-            }
-        }
+    // software pipeline, two register buffers: the LDS of candidate i+1 are in flight while
+    // candidate i is evaluated.  Columns past NC-1 are clamped loads whose results are unused.
+    float4 c0[D4], c1[D4];
+    cand_load<D4>(c0, row, xb);
+    for (int i = 0; i < NC; i += 2) {
+        cand_load<D4>(c1, row, xb + i + 1);
+        cand_eval<D4, KMASK>(c0, i, jbits, q, rowok, xlo, xspan, best, bpos);
+        cand_load<D4>(c0, row, xb + i + 2);
+        if (i + 1 < NC) cand_eval<D4, KMASK>(c1, i + 1, jbits, q, rowok, xlo, xspan, best, bpos);
     }
 }
 
