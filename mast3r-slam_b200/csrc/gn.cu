@@ -762,10 +762,16 @@ struct m3s_gn_plan {
     double* g = nullptr;            // [dim]
     double* dx = nullptr;           // [dim]
     Status* status = nullptr;
+    // assemble + factorisation (~90 launches) captured once per plan; all arguments are plan-constant
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;
+    bool graph_failed = false;
 };
 
 static void plan_free(m3s_gn_plan* p) {
     if (!p) return;
+    if (p->graph_exec) cudaGraphExecDestroy(p->graph_exec);
+    if (p->graph) cudaGraphDestroy(p->graph);
     cudaFree(p->poses); cudaFree(p->meta); cudaFree(p->partials); cudaFree(p->edge_blocks);
     cudaFree(p->blocks); cudaFree(p->list_edge); cudaFree(p->list_sign); cudaFree(p->free_kf);
     cudaFree(p->Hm); cudaFree(p->Ldiag); cudaFree(p->Linv); cudaFree(p->g); cudaFree(p->dx); cudaFree(p->status);
@@ -1008,11 +1014,9 @@ M3S_API int m3s_gn_assemble(m3s_gn_plan* plan, m3s_stream_t stream) {
     return M3S_OK;
 }
 
-M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_stream_t stream) {
-    M3S_REQUIRE(plan && gp, "gn_solve_update: null pointer");
-    if (plan->F == 0) return M3S_OK;
-    cudaStream_t st = as_stream(stream);
-    if (int rc = m3s_gn_assemble(plan, stream)) return rc;
+// assemble + blocked Cholesky of the augmented matrix, enqueued on `st`
+static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
+    if (int rc = m3s_gn_assemble(plan, reinterpret_cast<m3s_stream_t>(st))) return rc;
     const int np = plan->np;
     for (int k0 = 0; k0 < np; k0 += kNB) {
         const int rows_below = np + 1 - (k0 + kNB);  // incl. rhs row
@@ -1020,17 +1024,48 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
         chol_panel_kernel<<<grid, kTrsmRows, 0, st>>>(plan->status, plan->Hm, plan->Ldiag, plan->Linv, np, k0);
         if (int rc = launch_ok("chol_panel_kernel")) return rc;
         const int trailing = np - (k0 + kNB);
-        if (rows_below > 0 && trailing >= 0) {
+        if (trailing > 0) {
             const int tr = (rows_below + kSyrkTile - 1) / kSyrkTile;
-            const int tc = std::max(1, (trailing + kSyrkTile - 1) / kSyrkTile);
-            if (trailing > 0) {
-                chol_syrk_kernel<<<dim3(tc, tr), 256, 0, st>>>(plan->status, plan->Hm, np, k0);
-                if (int rc = launch_ok("chol_syrk_kernel")) return rc;
-            }
+            const int tc = (trailing + kSyrkTile - 1) / kSyrkTile;
+            chol_syrk_kernel<<<dim3(tc, tr), 256, 0, st>>>(plan->status, plan->Hm, np, k0);
+            if (int rc = launch_ok("chol_syrk_kernel")) return rc;
         }
     }
+    return M3S_OK;
+}
+
+// Capture the sequence once on a private stream (so a caller that is itself capturing is not
+// disturbed) and replay it with one cudaGraphLaunch per iteration.
+static void build_solve_graph(m3s_gn_plan* plan) {
+    cudaStream_t cs = nullptr;
+    if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess) { plan->graph_failed = true; cudaGetLastError(); return; }
+    bool ok = cudaStreamBeginCapture(cs, cudaStreamCaptureModeRelaxed) == cudaSuccess;
+    if (ok) {
+        const int rc = enqueue_assemble_factor(plan, cs);
+        cudaGraph_t g = nullptr;
+        const cudaError_t e = cudaStreamEndCapture(cs, &g);
+        ok = (rc == M3S_OK) && (e == cudaSuccess) && g;
+        if (ok) ok = cudaGraphInstantiate(&plan->graph_exec, g, 0) == cudaSuccess;
+        if (ok) plan->graph = g;
+        else if (g) cudaGraphDestroy(g);
+    }
+    if (!ok) { plan->graph_failed = true; plan->graph_exec = nullptr; cudaGetLastError(); }
+    cudaStreamDestroy(cs);
+}
+
+M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_stream_t stream) {
+    M3S_REQUIRE(plan && gp, "gn_solve_update: null pointer");
+    if (plan->F == 0) return M3S_OK;
+    cudaStream_t st = as_stream(stream);
+    const int np = plan->np;
+    if (!plan->graph_exec && !plan->graph_failed && np > 2 * kNB) build_solve_graph(plan);
+    if (plan->graph_exec) {
+        M3S_CUDA(cudaGraphLaunch(plan->graph_exec, st));
+    } else {
+        if (int rc = enqueue_assemble_factor(plan, st)) return rc;
+    }
     const size_t sh = sizeof(double) * np;
-    if (sh > 48 * 1024) {
+    if (sh > 40 * 1024) {
         M3S_CUDA(cudaFuncSetAttribute(gn_backsolve_update_kernel,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
     }
