@@ -466,27 +466,47 @@ __global__ void gn_pad_diag_kernel(const Status* __restrict__ status, double* __
 // ------------------------------------------------------------------------------------------------
 constexpr int kTrsmRows = 128;
 
-// 32x32 Cholesky in shared memory by the whole CTA (128 threads): per column one sqrt/reciprocal,
-// one column scale, one rank-1 update of the trailing block; 3 barriers per column.
-__device__ __forceinline__ void chol32_smem(double (*D)[kNB + 1], double* dinv, int* bad) {
+// 32x32 Cholesky in shared memory by the whole CTA (128 threads), ONE barrier per column:
+// every thread derives 1/d_jj itself (rsqrt, no broadcast step); the trailing update uses the
+// unscaled column,  D[r][c] -= D[r][j] D[c][j] / d_jj,  and the scaled column goes to a separate
+// array L (no write-after-read hazard inside a column step).  dinv[j] = 1 / L[j][j].
+__device__ __forceinline__ void chol32_smem(double (*D)[kNB + 1], double (*L)[kNB + 1], double* dinv,
+                                            int* bad) {
     const int tid = threadIdx.x;
     const int tc = tid & 31, tr = tid >> 5;
     for (int j = 0; j < kNB; ++j) {
-        if (tid == 0) {
-            double djj = D[j][j];
-            if (!((djj > 0.0) && (djj < 1e300))) { *bad = 1; djj = 1.0; }
-            const double ljj = sqrt(djj);
-            D[j][j] = ljj;
-            dinv[j] = 1.0 / ljj;
+        double djj = D[j][j];
+        if (!((djj > 0.0) && (djj < 1e300))) { if (tid == 0) *bad = 1; djj = 1.0; }
+        const double rs = rsqrt(djj);       // 1 / l_jj
+        const double inv_d = rs * rs;       // 1 / d_jj
+        if (tr == 0) {
+            // warp 0: column j of L (rows >= j), zeros above the diagonal
+            L[tc][j] = (tc > j) ? D[tc][j] * rs : ((tc == j) ? djj * rs : 0.0);
+            if (tc == j) dinv[j] = rs;
+        }
+        if (tc > j) {
+            const double cj = D[tc][j] * inv_d;
+            for (int r = j + 1 + tr; r < kNB; r += kTrsmRows / 32)
+                if (tc <= r) D[r][tc] -= D[r][j] * cj;
         }
         __syncthreads();
-        if (tid > j && tid < kNB) D[tid][j] *= dinv[j];
-        __syncthreads();
-        if (tc > j)
-            for (int r = j + 1 + tr; r < kNB; r += kTrsmRows / 32)
-                if (tc <= r) D[r][tc] -= D[r][j] * D[tc][j];
-        __syncthreads();
     }
+}
+
+// Column `lane` of the inverse of the lower-triangular 32x32 block L (shared memory), by forward
+// substitution with the column in registers; written as row-major Linv[r][lane].
+__device__ __forceinline__ void tri_inverse32(double (*L)[kNB + 1], const double* dinv,
+                                              double* __restrict__ out, int lane) {
+    double x[kNB];
+#pragma unroll
+    for (int r = 0; r < kNB; ++r) {
+        double sacc = (r == lane) ? 1.0 : 0.0;
+#pragma unroll
+        for (int k = 0; k < r; ++k) sacc -= L[r][k] * x[k];
+        x[r] = sacc * dinv[r];
+    }
+#pragma unroll
+    for (int r = 0; r < kNB; ++r) out[r * kNB + lane] = x[r];
 }
 
 // grid = row tiles of the panel below the diagonal block (incl. the rhs row) + 1 extra CTA that
@@ -495,39 +515,28 @@ __global__ void __launch_bounds__(kTrsmRows)
 chol_panel_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* __restrict__ Ldiag,
                   double* __restrict__ Linv, int np, int k0) {
     if (status->stopped | status->failed | status->chol_fail) return;
-    __shared__ double D[kNB][kNB + 1];
+    __shared__ double W[kNB][kNB + 1];  // working copy of the diagonal block
+    __shared__ double D[kNB][kNB + 1];  // its Cholesky factor (lower)
     __shared__ double dinv[kNB];
     __shared__ int bad;
     const int tid = threadIdx.x;
     for (int i = tid; i < kNB * kNB; i += blockDim.x) {
         const int r = i / kNB, c = i % kNB;
-        D[r][c] = (c <= r) ? Hm[(size_t)(k0 + r) * np + k0 + c] : 0.0;
+        W[r][c] = (c <= r) ? Hm[(size_t)(k0 + r) * np + k0 + c] : 0.0;
     }
     if (tid == 0) bad = 0;
     __syncthreads();
-    chol32_smem(D, dinv, &bad);
+    chol32_smem(W, D, dinv, &bad);
     if (bad) {
         if (blockIdx.x == 0 && tid == 0) status->chol_fail = 1;
         return;
     }
     if (blockIdx.x == gridDim.x - 1) {
-        // extra CTA: store L11 and its inverse.  Lane c of warp 0 solves L x = e_c (column c of
-        // L^-1) by forward substitution with the column in registers.
+        // extra CTA: publish L11; its inverse (for the back-substitution) is computed off the
+        // critical path by an extra CTA of the following syrk kernel, or here for the last panel.
         double* Ld = Ldiag + (size_t)(k0 / kNB) * kNB * kNB;
         for (int i = tid; i < kNB * kNB; i += blockDim.x) Ld[i] = D[i / kNB][i % kNB];
-        if (tid < 32) {
-            double x[kNB];
-#pragma unroll
-            for (int r = 0; r < kNB; ++r) {
-                double sacc = (r == tid) ? 1.0 : 0.0;
-#pragma unroll
-                for (int k = 0; k < r; ++k) sacc -= D[r][k] * x[k];
-                x[r] = sacc * dinv[r];
-            }
-            double* Li = Linv + (size_t)(k0 / kNB) * kNB * kNB;
-#pragma unroll
-            for (int r = 0; r < kNB; ++r) Li[r * kNB + tid] = x[r];  // row r, column tid
-        }
+        if (k0 + kNB >= np && tid < 32) tri_inverse32(D, dinv, Linv + (size_t)(k0 / kNB) * kNB * kNB, tid);
         return;
     }
     // rows below the diagonal block, including the rhs row np
@@ -551,9 +560,24 @@ chol_panel_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* 
 constexpr int kSyrkTile = 64;
 
 __global__ void __launch_bounds__(256)
-chol_syrk_kernel(const Status* __restrict__ status, double* __restrict__ Hm, int np, int k0) {
+chol_syrk_kernel(const Status* __restrict__ status, double* __restrict__ Hm,
+                 const double* __restrict__ Ldiag, double* __restrict__ Linv, int np, int k0) {
     if (status->stopped | status->failed | status->chol_fail) return;
     const int tr = blockIdx.y, tc = blockIdx.x;
+    if (tr == (int)gridDim.y - 1) {
+        // extra CTA row: block (0) inverts the diagonal factor of this step, concurrently with the
+        // trailing update (off the factorisation's critical path)
+        if (tc != 0) return;
+        __shared__ double Ls[kNB][kNB + 1];
+        __shared__ double di[kNB];
+        const double* Ld = Ldiag + (size_t)(k0 / kNB) * kNB * kNB;
+        for (int i = threadIdx.x; i < kNB * kNB; i += blockDim.x) Ls[i / kNB][i % kNB] = Ld[i];
+        __syncthreads();
+        if (threadIdx.x < kNB) di[threadIdx.x] = 1.0 / Ls[threadIdx.x][threadIdx.x];
+        __syncthreads();
+        if (threadIdx.x < 32) tri_inverse32(Ls, di, Linv + (size_t)(k0 / kNB) * kNB * kNB, threadIdx.x);
+        return;
+    }
     if (tc > tr) return;
     const int base = k0 + kNB;
     const int r0 = base + tr * kSyrkTile, c0 = base + tc * kSyrkTile;
@@ -1027,7 +1051,7 @@ static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
         if (trailing > 0) {
             const int tr = (rows_below + kSyrkTile - 1) / kSyrkTile;
             const int tc = (trailing + kSyrkTile - 1) / kSyrkTile;
-            chol_syrk_kernel<<<dim3(tc, tr), 256, 0, st>>>(plan->status, plan->Hm, np, k0);
+            chol_syrk_kernel<<<dim3(tc, tr + 1), 256, 0, st>>>(plan->status, plan->Hm, plan->Ldiag, plan->Linv, np, k0);
             if (int rc = launch_ok("chol_syrk_kernel")) return rc;
         }
     }
