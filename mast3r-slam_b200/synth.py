@@ -348,9 +348,14 @@ def make_graph_torch(device, seed=0, num_kf=200, num_loops=103, h=384, w=512, no
     idx = torch.empty((ne, n), dtype=torch.int32, device=device)
     for r, k in enumerate(range(eb, ee)):
         idx[r] = ((base + int(shifts[jj[k]] - shifts[ii[k]])) % n).int()
-    valid = (torch.rand((ne, n), generator=gen, device=device) < valid_frac).to(torch.uint8)
-    Q = 1.2 + 2.8 * torch.rand((ne, n), generator=gen, device=device)
     Cs = 1.0 + 10.0 * torch.rand((num_kf, n), generator=gen, device=device)
+    # per-edge seeds: a rank that materialises only its edge rows sees the same rows as a full build
+    valid = torch.empty((ne, n), dtype=torch.uint8, device=device)
+    Q = torch.empty((ne, n), dtype=torch.float32, device=device)
+    for r, k in enumerate(range(eb, ee)):
+        gen.manual_seed(900000 + 1000 * seed + k)
+        valid[r] = (torch.rand(n, generator=gen, device=device) < valid_frac).to(torch.uint8)
+        Q[r] = 1.2 + 2.8 * torch.rand(n, generator=gen, device=device)
     return dict(Twc=Twc.astype(np.float32), Twc_gt=Twc_gt.astype(np.float32), Xs=Xs, Cs=Cs, ii=ii, jj=jj,
                 idx=idx, valid=valid, Q=Q, K4=np.array([fx, fy, cx0, cy0], np.float32), img_size=(w, h),
                 edge_range=(eb, ee))
