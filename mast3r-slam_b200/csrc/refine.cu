@@ -40,9 +40,21 @@ struct Acc4 {
     float2 xy, zw;
     __device__ __forceinline__ Acc4() : xy(make_float2(0.f, 0.f)), zw(make_float2(0.f, 0.f)) {}
     __device__ __forceinline__ void fma4(const float4& a, const float4& b) {
-#ifdef M3S_REFINE_SCALAR_FMA  // A/B experiment: same arithmetic with four scalar FFMA
+#if defined(M3S_REFINE_SCALAR_FMA)  // A/B experiment: same arithmetic with four scalar FFMA
         xy.x = fmaf(a.x, b.x, xy.x); xy.y = fmaf(a.y, b.y, xy.y);
         zw.x = fmaf(a.z, b.z, zw.x); zw.y = fmaf(a.w, b.w, zw.y);
+#elif defined(M3S_REFINE_ASM_FMA)  // A/B experiment: volatile asm keeps the interleaved chain order
+        unsigned long long axy, azw, bxy, bzw, cxy, czw;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(axy) : "f"(a.x), "f"(a.y));
+        asm("mov.b64 %0, {%1, %2};" : "=l"(azw) : "f"(a.z), "f"(a.w));
+        asm("mov.b64 %0, {%1, %2};" : "=l"(bxy) : "f"(b.x), "f"(b.y));
+        asm("mov.b64 %0, {%1, %2};" : "=l"(bzw) : "f"(b.z), "f"(b.w));
+        asm("mov.b64 %0, {%1, %2};" : "=l"(cxy) : "f"(xy.x), "f"(xy.y));
+        asm("mov.b64 %0, {%1, %2};" : "=l"(czw) : "f"(zw.x), "f"(zw.y));
+        asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(cxy) : "l"(axy), "l"(bxy));
+        asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(czw) : "l"(azw), "l"(bzw));
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(xy.x), "=f"(xy.y) : "l"(cxy));
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(zw.x), "=f"(zw.y) : "l"(czw));
 #else
         xy = __ffma2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y), xy);
         zw = __ffma2_rn(make_float2(a.z, a.w), make_float2(b.z, b.w), zw);

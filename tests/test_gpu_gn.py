@@ -216,3 +216,56 @@ def test_l2_global_opt_entry_points(K, oracle, synth):
     ref = oracle.gauss_newton_calib(g["Twc"], g["Xs"], g["Cs"], g["K4"], *two, g["img_size"],
                                     sigma_pixel=1.0, sigma_depth=10.0, max_iter=10, delta_thresh=1e-3)
     assert upd_err(out, ref, g["Twc"]) <= REL
+
+
+def _torch_graph_to_numpy(g):
+    return dict(Twc=g["Twc"], Xs=g["Xs"].cpu().numpy(), Cs=g["Cs"].cpu().numpy(), ii=g["ii"], jj=g["jj"],
+                idx=g["idx"].cpu().numpy(), valid=g["valid"].cpu().numpy().astype(bool),
+                Q=g["Q"].cpu().numpy())
+
+
+def test_full_size_config3_rays(K, oracle, synth):
+    """BASELINE.json config 3: gauss_newton_rays, 10 keyframes / 40 directed edges, N = 196 608,
+    full size against the (OpenMP) oracle"""
+    import torch
+    g = synth.make_graph_torch(torch.device("cuda", 0), 3, 10, 3, 384, 512)
+    assert len(g["ii"]) == 40 and g["Xs"].shape[1] == 196608
+    out = K.gauss_newton_rays(torch.from_numpy(g["Twc"]).cuda(), g["Xs"], g["Cs"], g["ii"], g["jj"],
+                              g["idx"], g["valid"], g["Q"], max_iter=10)
+    h = _torch_graph_to_numpy(g)
+    ref = oracle.gauss_newton_rays(*gargs(h), max_iter=10)
+    assert upd_err(out.cpu().numpy(), ref, h["Twc"]) <= REL
+    assert np.abs(ref - g["Twc_gt"]).max() < 0.2 * np.abs(h["Twc"] - g["Twc_gt"]).max()
+
+
+def test_full_size_config4_calib_sequence(K, oracle, synth):
+    """BASELINE.json config 4: tracking-style 2-keyframe calibrated solves (keyframe pinned, frame
+    free, both edge directions) at 512x384 with known intrinsics, a short synthetic sequence"""
+    import torch
+    for frame in range(3):
+        g = synth.make_graph_torch(torch.device("cuda", 0), 40 + frame, 2, 0, 384, 512)
+        assert len(g["ii"]) == 2
+        out = K.gauss_newton_calib(torch.from_numpy(g["Twc"]).cuda(), g["Xs"], g["Cs"], g["K4"], g["ii"],
+                                   g["jj"], g["idx"], g["valid"], g["Q"], g["img_size"], pixel_border=0,
+                                   z_eps=0.0, sigma_pixel=1.0, sigma_depth=10.0, max_iter=10)
+        h = _torch_graph_to_numpy(g)
+        ref = oracle.gauss_newton_calib(h["Twc"], h["Xs"], h["Cs"], g["K4"], h["ii"], h["jj"], h["idx"],
+                                        h["valid"], h["Q"], g["img_size"], pixel_border=0, z_eps=0.0,
+                                        sigma_pixel=1.0, sigma_depth=10.0, max_iter=10)
+        assert upd_err(out.cpu().numpy(), ref, h["Twc"]) <= REL
+        assert np.array_equal(out.cpu().numpy()[0], h["Twc"][0])  # pinned keyframe untouched
+
+
+def test_full_size_config5_points(K, oracle, synth):
+    """BASELINE.json config 5 at FULL size: 200 keyframes / 1000 directed edges / 196 608 points,
+    gauss_newton_points, 2 iterations against the oracle (2.4 GB of inputs)"""
+    import torch
+    g = synth.make_graph_torch(torch.device("cuda", 0), 0, 200, 103, 384, 512)
+    assert len(g["ii"]) == 1000
+    out = K.gauss_newton_points(torch.from_numpy(g["Twc"]).cuda(), g["Xs"], g["Cs"], g["ii"], g["jj"],
+                                g["idx"], g["valid"], g["Q"], max_iter=2)
+    h = _torch_graph_to_numpy(g)
+    del g
+    torch.cuda.empty_cache()
+    ref = oracle.gauss_newton_points(*gargs(h), max_iter=2)
+    assert upd_err(out.cpu().numpy(), ref, h["Twc"]) <= REL

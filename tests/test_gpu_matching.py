@@ -257,3 +257,26 @@ def test_refine_tiled_path(K, oracle, synth, hw):
     out = K.refine_matches(np.ones_like(D11), D21, jitter.astype(np.int32), 3, 0)
     ref = oracle.refine_matches(np.ones_like(D11), D21, jitter.astype(np.int32), 3, 0)
     assert np.array_equal(out, ref)
+
+
+def test_full_size_config2_batch_properties(K, oracle, synth):
+    """BASELINE.json config 2: a multi-pair batch at 512x384 in one call.  The whole batch is
+    checked through size-independent properties; 2 of its pairs bit-exactly against the oracle;
+    and batching itself must not change any pair's result (pairs are independent)."""
+    import torch
+    B = 8
+    ps = synth.make_pairs_torch(range(B), torch.device("cuda", 0), 384, 512, 24, "dyadic")
+    idx, valid = K.match_iterative_proj_device(ps["X11"], ps["X21"], ps["D11"], ps["D21"])
+    idx, valid = idx.cpu().numpy(), valid.cpu().numpy()
+    assert idx.shape == (B, 196608) and valid.shape == (B, 196608, 1)
+    x, y = idx % 512, idx // 512
+    ok = valid[..., 0]
+    assert ((x[ok] >= 0) & (x[ok] < 512) & (y[ok] >= 0) & (y[ok] < 384)).all()
+    assert ok.mean() > 0.9
+    for b in (0, B - 1):
+        one = {k: v[b:b + 1].cpu().numpy() for k, v in ps.items()}
+        idx_o, valid_o = oracle.match_iterative_proj(one["X11"], one["X21"], one["D11"], one["D21"])
+        assert np.array_equal(idx[b:b + 1], idx_o) and np.array_equal(valid[b:b + 1], valid_o)
+        i1, v1 = K.match_iterative_proj_device(ps["X11"][b:b + 1], ps["X21"][b:b + 1], ps["D11"][b:b + 1],
+                                               ps["D21"][b:b + 1])
+        assert np.array_equal(i1.cpu().numpy(), idx[b:b + 1]) and np.array_equal(v1.cpu().numpy(), valid[b:b + 1])
