@@ -90,6 +90,69 @@ def test_iter_proj_edge_cases(K, oracle, synth):
     assert np.array_equal(pt.cpu().numpy(), po) and np.array_equal(vt.cpu().numpy(), vo)
 
 
+@pytest.mark.parametrize("impl", ["quad", "tile", "generic"])
+@pytest.mark.parametrize("hw", [(48, 64), (37, 52), (16, 36), (50, 70)])
+def test_iter_proj_full_frame_impls(K, oracle, synth, monkeypatch, impl, hw):
+    """Full-frame queries (N == H*W) through each implementation (2x2-points-per-thread quad kernel
+    with its eviction queue, one-point tile kernel, generic kernel): coherent flow, incoherent
+    starts (evictions / global fallback), starts outside the image, NaN starts, ragged sizes
+    (partial tiles, odd H, W % 4 != 0 falls back by itself), several iteration counts, B = 2."""
+    monkeypatch.setenv("M3S_ITER_PROJ_IMPL", impl)
+    h, w = hw
+    b = 2
+    pairs = [synth.make_pair(7 + i, h, w, 24, "dyadic") for i in range(b)]
+    X11 = np.stack([q["X11"] for q in pairs])
+    X21 = np.stack([q["X21"] for q in pairs])
+    rays, pts, p0 = oracle.prep_for_iter_proj(X11, X21, None)
+    rng = np.random.default_rng(h * 1000 + w)
+    starts = {"identity": p0}
+    jit = p0 + rng.uniform(-1.5, 1.5, p0.shape).astype(np.float32)
+    starts["jitter"] = jit
+    wild = jit.copy()
+    sel = rng.random(p0.shape[:2]) < 0.05
+    wild[sel] = np.stack([rng.uniform(-6, w + 6, sel.sum()), rng.uniform(-6, h + 6, sel.sum())], -1)
+    wild[0, 3] = np.nan
+    wild[1, 10, 1] = np.nan
+    starts["wild"] = wild.astype(np.float32)
+    starts["random"] = np.stack([rng.uniform(0, w, p0.shape[:2]), rng.uniform(0, h, p0.shape[:2])], -1).astype(np.float32)
+    for name, st in starts.items():
+        for it, lam in ((10, 1e-8), (3, 1e-4), (1, 1e-8)):
+            p, v = K.iter_proj(rays, pts, st, it, lam, 1e-6)
+            if name == "wild":  # numpy cannot index with NaN positions: compare the finite points
+                fin = np.isfinite(st).all(-1)
+                st_o = np.where(fin[..., None], st, 0.0).astype(np.float32)
+                po, vo = oracle.iter_proj(rays, pts, st_o, it, lam, 1e-6)
+                assert np.array_equal(p[fin], po[fin]) and np.array_equal(v[fin], vo[fin]), (name, it)
+                assert not v[~fin].any()
+            else:
+                po, vo = oracle.iter_proj(rays, pts, st, it, lam, 1e-6)
+                assert np.array_equal(v, vo), (name, it)
+                assert np.array_equal(p, po), (name, it, int((p != po).any(-1).sum()))
+    # the reference's own random ray images (incoherent gradients: large steps, many evictions)
+    rr, pp, q0 = synth.reference_like_iter_proj(3, b, h, w, h * w)
+    p, v = K.iter_proj(rr, pp, q0, 10, 1e-8, 1e-6)
+    po, vo = oracle.iter_proj(rr, pp, q0, 10, 1e-8, 1e-6)
+    assert np.array_equal(p, po) and np.array_equal(v, vo)
+
+
+def test_iter_proj_global_break_full_frame(K, oracle, synth, monkeypatch):
+    """global early exit (kernels.py:239-241) through the quad kernel and its queue: a threshold
+    between two iterations' maxima must stop every point at the same iteration as the oracle."""
+    h, w = 32, 64
+    pair = synth.make_pair(11, h, w, 24, "dyadic")
+    rays, pts, p0 = oracle.prep_for_iter_proj(pair["X11"][None], pair["X21"][None], None)
+    p0 = p0 + np.random.default_rng(0).uniform(-0.4, 0.4, p0.shape).astype(np.float32)
+    ref = [oracle.iter_proj(rays, pts, p0, k, 1e-8, 0.0)[0] for k in range(0, 9)]
+    step = [float(np.sqrt(((ref[k + 1] - ref[k]).astype(np.float32) ** 2).sum(-1)).max()) for k in range(8)]
+    for impl in ("quad", "tile", "generic"):
+        monkeypatch.setenv("M3S_ITER_PROJ_IMPL", impl)
+        for k in (2, 5):
+            thr = 0.5 * (step[k] + step[k - 1]) if step[k] < step[k - 1] else step[k] * 1.01
+            p, v = K.iter_proj(rays, pts, p0, 8, 1e-8, thr)
+            po, vo = oracle.iter_proj(rays, pts, p0, 8, 1e-8, thr)
+            assert np.array_equal(p, po) and np.array_equal(v, vo), (impl, k)
+
+
 def test_prep_and_tail_vs_oracle(K, oracle, synth):
     pair = synth.make_pair(2, 40, 56)
     X11, X21 = pair["X11"][None], pair["X21"][None]
