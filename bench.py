@@ -42,6 +42,14 @@ ALG_BYTES_PATH = 257                             # fused iter_p
 GN_KF, GN_LOOPS = 200, 103
 
 
+def load_traffic():
+    """measured DRAM traffic per unit (ncu --set full captures, profiles/traffic.json)"""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+    except Exception:
+        return {}
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -203,8 +211,8 @@ def main():
     # ---- roofline of the dominant kernel (per launch = one 64-pair batch) ------------------------
     units = B * NPIX
     kinfo = {
-        "iter_proj_kernel": {"ms": t_ip_ms, "alg_bytes": ALG_BYTES_ITER_PROJ * units},
-        "refine_kernel": {"ms": t_rf_ms, "alg_bytes": ALG_BYTES_REFINE * units},
+        "iter_proj_tile_kernel": {"ms": t_ip_ms, "alg_bytes": ALG_BYTES_ITER_PROJ * units},
+        "refine_tiled_kernel": {"ms": t_rf_ms, "alg_bytes": ALG_BYTES_REFINE * units},
     }
     for v in kinfo.values():
         v["gbs"] = v["alg_bytes"] / (v["ms"] * 1e-3) / 1e9
@@ -212,7 +220,8 @@ def main():
     path_gbs = ALG_BYTES_PATH * units / ((t_ip_ms + t_rf_ms) * 1e-3) / 1e9
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": round(kinfo[dom]["gbs"], 1), "peak": peak,
-        "unit": "GB/s", "frac": round(kinfo[dom]["gbs"] / peak, 4), "traffic": None,
+        "unit": "GB/s", "frac": round(kinfo[dom]["gbs"] / peak, 4),
+        "traffic": (round(load_traffic()[dom]["dram_bytes_per_px"] * units) if dom in load_traffic() else None),
         "peak_source": peak_src,
         "kernels": {k: {"ms_per_launch": round(v["ms"], 4), "alg_bytes_per_launch": v["alg_bytes"],
                         "achieved_gbs": round(v["gbs"], 1), "frac": round(v["gbs"] / peak, 4)}

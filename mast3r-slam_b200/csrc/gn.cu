@@ -227,7 +227,13 @@ gn_accum_kernel(const Status* __restrict__ status, KernelParams P, const double*
         ec_s.s_inv = si_inv;
     }
     __syncthreads();
+#ifdef M3S_GN_EC_REGS
     const EdgeConst ec = ec_s;
+#else
+    // the 13 per-edge constants stay in shared memory and are re-read every trip (LDS.64, shared by
+    // the 4 points of the trip): 26 fewer live registers next to the 58 accumulator registers
+    const EdgeConst& ec = ec_s;
+#endif
 
     double acc[NA];
 #pragma unroll
@@ -255,6 +261,9 @@ gn_accum_kernel(const Status* __restrict__ status, KernelParams P, const double*
         const float4* __restrict__ c4p = reinterpret_cast<const float4*>(Cj);
         const float4* __restrict__ x4p = reinterpret_cast<const float4*>(Xj);
         for (long long g = (n0 >> 2) + threadIdx.x; g < (n1 >> 2); g += kAccThreads) {
+#ifndef M3S_GN_EC_REGS
+            asm volatile("" ::: "memory");  // keep the per-edge constants out of loop-carried registers
+#endif
             const uchar4 v4 = __ldg(v4p + g);
             const float4 q4 = __ldg(q4p + g);
             const int4 i4 = __ldg(i4p + g);

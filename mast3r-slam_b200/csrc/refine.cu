@@ -164,19 +164,22 @@ __device__ __forceinline__ void cp_async_wait_all() {
 // conflict-free LDS.128 and is reused from registers by every active query.  Lanes / queries for
 // which the candidate is outside their own (2r+1)^2 window compute a dot product that the compare
 // predicate discards.  Position packed as (row << 16) | col in lane-relative window coordinates.
-template <int D4, unsigned KMASK>
-__device__ __forceinline__ void cand_eval(const float4 (&c)[D4], int i, int jbits,
-                                          const float4 (&q)[kQ][D4], const bool (&rowok)[kQ],
+//
+// Candidates are evaluated TWO AT A TIME (columns i, i+1): with 8 warps per SM the FMA pipe only
+// stays busy if every warp carries enough independent FFMA2 chains, and the top / bottom rows of
+// the union window serve a single query (2 chains).  A pair gives >= 4 chains for every mask.  The
+// pair after the current one is fetched chunk by chunk into the registers the current pair has
+// just finished with (c[d] is dead after chunk d), so its LDS latency is covered by the remaining
+// chunks and the score epilogue -- a software pipeline without a second register buffer.
+template <int D4>
+__device__ __forceinline__ const float4* cand_ptr(const float4* __restrict__ row, int col) {
+    return row + min(col, kWinX - 1) * TiledCfg<D4>::pitch4;
+}
+
+template <unsigned KMASK>
+__device__ __forceinline__ void cand_pick(const Acc4 (&a)[kQ], int pos, int i, const bool (&rowok)[kQ],
                                           const int (&xlo)[kQ], const unsigned (&xspan)[kQ],
                                           float (&best)[kQ], int (&bpos)[kQ]) {
-    Acc4 a[kQ];
-    // chunk-outer / query-inner: 2 x popcount(KMASK) independent FFMA2 chains interleaved
-#pragma unroll
-    for (int d = 0; d < D4; ++d)
-#pragma unroll
-        for (int k = 0; k < kQ; ++k)
-            if ((KMASK >> k) & 1u) a[k].fma4(q[k][d], c[d]);
-    const int pos = jbits | i;
 #pragma unroll
     for (int k = 0; k < kQ; ++k) {
         if ((KMASK >> k) & 1u) {
@@ -189,30 +192,50 @@ __device__ __forceinline__ void cand_eval(const float4 (&c)[D4], int i, int jbit
     }
 }
 
-template <int D4>
-__device__ __forceinline__ void cand_load(float4 (&c)[D4], const float4* __restrict__ row, int col) {
-    constexpr int P4 = TiledCfg<D4>::pitch4;
-    const float4* __restrict__ cp = row + min(col, kWinX - 1) * P4;
+// evaluate the pair (c0 = column i, c1 = column i+1; c1 skipped when !SECOND) and refill c0 / c1
+// from n0 / n1 (the next pair) as their chunks retire
+template <int D4, unsigned KMASK, bool SECOND>
+__device__ __forceinline__ void pair_eval(float4 (&c0)[D4], float4 (&c1)[D4],
+                                          const float4* __restrict__ n0, const float4* __restrict__ n1,
+                                          int i, int jbits, const float4 (&q)[kQ][D4],
+                                          const bool (&rowok)[kQ], const int (&xlo)[kQ],
+                                          const unsigned (&xspan)[kQ], float (&best)[kQ],
+                                          int (&bpos)[kQ]) {
+    Acc4 a0[kQ], a1[kQ];
 #pragma unroll
-    for (int d = 0; d < D4; ++d) c[d] = cp[d];
+    for (int d = 0; d < D4; ++d) {
+#pragma unroll
+        for (int k = 0; k < kQ; ++k) {
+            if ((KMASK >> k) & 1u) {
+                a0[k].fma4(q[k][d], c0[d]);
+                if (SECOND) a1[k].fma4(q[k][d], c1[d]);
+            }
+        }
+        c0[d] = n0[d];
+        c1[d] = n1[d];
+    }
+    cand_pick<KMASK>(a0, jbits | i, i, rowok, xlo, xspan, best, bpos);  // scan order: i before i+1
+    if (SECOND) cand_pick<KMASK>(a1, jbits | (i + 1), i + 1, rowok, xlo, xspan, best, bpos);
 }
 
+// `row` = this window row, `nrow` = the next one (its first pair is prefetched by the last pair here)
 template <int D4, unsigned KMASK>
-__device__ __forceinline__ void row_scan(const float4* __restrict__ row, int xb, int NC, int j,
+__device__ __forceinline__ void row_scan(const float4* __restrict__ row, const float4* __restrict__ nrow,
+                                         int xb, int NC, int j, float4 (&c0)[D4], float4 (&c1)[D4],
                                          const float4 (&q)[kQ][D4], const bool (&rowok)[kQ],
                                          const int (&xlo)[kQ], const unsigned (&xspan)[kQ],
                                          float (&best)[kQ], int (&bpos)[kQ]) {
     const int jbits = j << 16;
-    // software pipeline, two register buffers: the LDS of candidate i+1 are in flight while
-    // candidate i is evaluated.  Columns past NC-1 are clamped loads whose results are unused.
-    float4 c0[D4], c1[D4];
-    cand_load<D4>(c0, row, xb);
-    for (int i = 0; i < NC; i += 2) {
-        cand_load<D4>(c1, row, xb + i + 1);
-        cand_eval<D4, KMASK>(c0, i, jbits, q, rowok, xlo, xspan, best, bpos);
-        cand_load<D4>(c0, row, xb + i + 2);
-        if (i + 1 < NC) cand_eval<D4, KMASK>(c1, i + 1, jbits, q, rowok, xlo, xspan, best, bpos);
-    }
+    int i = 0;
+    for (; i + 2 < NC; i += 2)
+        pair_eval<D4, KMASK, true>(c0, c1, cand_ptr<D4>(row, xb + i + 2), cand_ptr<D4>(row, xb + i + 3),
+                                   i, jbits, q, rowok, xlo, xspan, best, bpos);
+    const float4* __restrict__ n0 = cand_ptr<D4>(nrow, xb);
+    const float4* __restrict__ n1 = cand_ptr<D4>(nrow, xb + 1);
+    if (i + 1 < NC)
+        pair_eval<D4, KMASK, true>(c0, c1, n0, n1, i, jbits, q, rowok, xlo, xspan, best, bpos);
+    else
+        pair_eval<D4, KMASK, false>(c0, c1, n0, n1, i, jbits, q, rowok, xlo, xspan, best, bpos);
 }
 
 template <int D4, typename PT>
@@ -347,6 +370,14 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
             if (any) { nr = max(nr, yz - Y0 + 1); nc = max(nc, xz - X0 + 1); }
         }
         const int NR = __reduce_max_sync(0xffffffffu, nr), NC = __reduce_max_sync(0xffffffffu, nc);
+        float4 c0[D4], c1[D4];  // the candidate pair in flight (columns i, i+1 of the current row)
+        {
+            const float4* __restrict__ r0 = tile + (min(yb, kWinY - 1) * kWinX) * P4;
+            const float4* __restrict__ p0 = cand_ptr<D4>(r0, xb);
+            const float4* __restrict__ p1 = cand_ptr<D4>(r0, xb + 1);
+#pragma unroll
+            for (int d = 0; d < D4; ++d) { c0[d] = p0[d]; c1[d] = p1[d]; }
+        }
         for (int j = 0; j < NR; ++j) {
             bool rowok[kQ];
             unsigned kmask = 0;
@@ -356,9 +387,16 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
                 if (__any_sync(0xffffffffu, rowok[k])) kmask |= 1u << k;
             }
             const float4* __restrict__ row = tile + (min(yb + j, kWinY - 1) * kWinX) * P4;
-#define M3S_ROW(MASK) case MASK: row_scan<D4, MASK>(row, xb, NC, j, q, rowok, xlo, xspan, best, bpos); break
+            const float4* __restrict__ nrow = tile + (min(yb + j + 1, kWinY - 1) * kWinX) * P4;
+#define M3S_ROW(MASK) case MASK: row_scan<D4, MASK>(row, nrow, xb, NC, j, c0, c1, q, rowok, xlo, xspan, best, bpos); break
             switch (kmask) {  // warp-uniform
-                case 0: break;
+                case 0: {  // no query uses this row: just advance the pipeline to the next row
+                    const float4* __restrict__ p0 = cand_ptr<D4>(nrow, xb);
+                    const float4* __restrict__ p1 = cand_ptr<D4>(nrow, xb + 1);
+#pragma unroll
+                    for (int d = 0; d < D4; ++d) { c0[d] = p0[d]; c1[d] = p1[d]; }
+                    break;
+                }
                 M3S_ROW(1); M3S_ROW(2); M3S_ROW(3); M3S_ROW(4); M3S_ROW(5); M3S_ROW(6); M3S_ROW(7);
                 M3S_ROW(8); M3S_ROW(9); M3S_ROW(10); M3S_ROW(11); M3S_ROW(12); M3S_ROW(13);
                 M3S_ROW(14); M3S_ROW(15);
