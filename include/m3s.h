@@ -107,6 +107,25 @@ int m3s_match_iterative_proj(const float* X11, const float* X21, const float* D1
                              int dilation_max, float dist_thresh, void* workspace,
                              size_t workspace_bytes, m3s_stream_t stream);
 
+/* ---- factor-graph host steps (between match() and gauss_newton_*()) --------------------------- */
+
+/* Replaces constrain_points_to_ray (geometry.py:273-302) = backproject (geometry.py:229-246) of
+ * the pixel grid with each point's own depth:  x = (u - cx) / fx * z,  y = (v - cy) / fy * z.
+ *   Xs [B,H*W,3] f32 (device), K4_host = (fx, fy, cx, cy) on the HOST -> out [B,H*W,3] (may alias Xs) */
+int m3s_constrain_points_to_ray(const float* Xs, const float* K4_host, float* out, int B, int H,
+                                int W, m3s_stream_t stream);
+
+/* Replaces the confidence / match-fraction step of FactorGraph.add_factors
+ * (global_opt.py:86-104):  Qj = sqrt(Qii[e, idx[e,n]] * Qji[e,n]),
+ * valid = valid_match & (Qj > Q_conf), valid_count[e] = sum_n valid.
+ *   Qii, Qji [E,N] f32; idx [E,N] i32; valid_match [E,N] u8
+ *   -> Qj_out [E,N] f32, valid_out [E,N] u8 (or NULL), valid_count [E] i32.
+ * idx outside [0,N) (an error in the reference) gives Qj = 0, valid = 0. */
+int m3s_edge_confidence(const float* Qii, const float* Qji, const int32_t* idx,
+                        const uint8_t* valid_match, float q_conf, float* Qj_out,
+                        uint8_t* valid_out, int32_t* valid_count, int E, long long N,
+                        m3s_stream_t stream);
+
 /* ---- Gauss-Newton -------------------------------------------------------------------------- */
 
 /* Scalars of gauss_newton_{rays,points,calib} (backends/mpsgraph/kernels.py:262-279, 325-346,

@@ -22,6 +22,7 @@ SOURCES = {
     "match_exact.cu": ["-fmad=false"],
     "refine.cu": [],
     "gn.cu": [],
+    "graph_host.cu": ["-fmad=false"],
 }
 
 

@@ -26,7 +26,7 @@ from ._lib import GNParams, M3SError  # noqa: F401
 
 __all__ = ["is_available", "iter_proj", "refine_matches", "gauss_newton_rays",
            "gauss_newton_points", "gauss_newton_calib", "match_iterative_proj_device",
-           "prep_for_iter_proj", "match_tail", "GNPlan"]
+           "prep_for_iter_proj", "match_tail", "GNPlan", "constrain_points_to_ray", "edge_confidence"]
 
 _workspaces: dict = {}
 
@@ -90,6 +90,56 @@ def _out(t, as_numpy, np_dtype=None):
         return t
     a = t.cpu().numpy()
     return a.astype(np_dtype) if np_dtype is not None and a.dtype != np_dtype else a
+
+
+# ---------------------------------------------------------------------------------------------
+# factor-graph host steps (global_opt.py:86-104, geometry.py:273-302)
+# ---------------------------------------------------------------------------------------------
+def _k4(K):
+    k = np.asarray(K.detach().cpu().numpy() if isinstance(K, torch.Tensor) else K, dtype=np.float32)
+    if k.shape == (3, 3):
+        k = np.array([k[0, 0], k[1, 1], k[0, 2], k[1, 2]], dtype=np.float32)
+    if k.shape != (4,):
+        raise M3SError("K must be a 3x3 matrix or (fx, fy, cx, cy)")
+    return (C.c_float * 4)(*[float(v) for v in k])
+
+
+def constrain_points_to_ray(img_size, Xs, K):
+    """geometry.py:273-302: re-project every point onto its own pixel ray at its own depth.
+    img_size = (H, W); Xs [B,H*W,3]; K 3x3 or (fx,fy,cx,cy)."""
+    as_np = _wants_numpy(Xs)
+    dev = _device(Xs)
+    h, w = int(img_size[0]), int(img_size[1])
+    x = _dev(Xs, torch.float32, dev)
+    if x.dim() != 3 or x.shape[1] != h * w or x.shape[2] != 3:
+        raise M3SError("constrain_points_to_ray: Xs must be [B,H*W,3]")
+    out = torch.empty_like(x)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.load().m3s_constrain_points_to_ray(_ptr(x), _k4(K), _ptr(out), x.shape[0], h, w,
+                                                         _stream(dev)), "constrain_points_to_ray")
+    return _out(out, as_np)
+
+
+def edge_confidence(Qii, Qji, idx, valid_match, Q_conf):
+    """global_opt.py:86-104 -> (Qj [E,N,1] f32, valid [E,N,1] bool, match_frac [E] f32)."""
+    as_np = _wants_numpy(Qii, Qji, idx, valid_match)
+    dev = _device(Qii, Qji, idx, valid_match)
+    qi = _dev(Qii, torch.float32, dev)
+    e, n = qi.shape[0], qi.shape[1]
+    qi = qi.reshape(e, n)
+    qj = _dev(Qji, torch.float32, dev).reshape(e, n)
+    ix = _dev(idx, torch.int32, dev).reshape(e, n)
+    vm = _dev(valid_match, torch.bool, dev).reshape(e, n).view(torch.uint8)
+    q_out = torch.empty((e, n), dtype=torch.float32, device=dev)
+    v_out = torch.empty((e, n), dtype=torch.uint8, device=dev)
+    cnt = torch.empty((e,), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.load().m3s_edge_confidence(_ptr(qi), _ptr(qj), _ptr(ix), _ptr(vm), float(Q_conf),
+                                                 _ptr(q_out), _ptr(v_out), _ptr(cnt), e, n, _stream(dev)),
+                   "edge_confidence")
+    frac = cnt.to(torch.float32) / float(max(n, 1))
+    return (_out(q_out.reshape(e, n, 1), as_np), _out(v_out.view(torch.bool).reshape(e, n, 1), as_np),
+            _out(frac, as_np))
 
 
 # ---------------------------------------------------------------------------------------------

@@ -38,3 +38,23 @@ def match(X11, X21, D11, D21, idx_1_to_2_init=None):
             "outside the accelerated path; set matching.use_simple=False (set_config) to use "
             "match_iterative_proj")
     return match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init)
+
+
+def match_symmetric(Xii, Xji, Xjj, Xij, Dii, Dji, Djj, Dij, idx_i2j_init=None, idx_j2i_init=None):
+    """Both directions of a keyframe pair batch in ONE enqueue (what mast3r_match_symmetric,
+    mast3r_utils.py:503-569, is meant to do once the decoder has produced the four pointmaps; the
+    reference's version is an identity-match stub).  Inputs [B,H,W,3] / [B,H,W,D]; the i->j and
+    j->i problems are stacked on the batch axis, so the pairs of a batch and the two directions all
+    run in the same kernel launches.  Returns (idx_i2j, idx_j2i, valid_match_j, valid_match_i)."""
+    import numpy as np
+    import torch
+    cat = (lambda a, b: torch.cat([a, b])) if isinstance(Xii, torch.Tensor) else \
+          (lambda a, b: np.concatenate([np.asarray(a), np.asarray(b)]))
+    init = None
+    if idx_i2j_init is not None or idx_j2i_init is not None:
+        if idx_i2j_init is None or idx_j2i_init is None:
+            raise ValueError("match_symmetric: give both initialisations or neither")
+        init = cat(idx_i2j_init, idx_j2i_init)
+    idx, valid = match_iterative_proj(cat(Xii, Xjj), cat(Xji, Xij), cat(Dii, Djj), cat(Dji, Dij), init)
+    b = Xii.shape[0]
+    return idx[:b], idx[b:], valid[:b], valid[b:]

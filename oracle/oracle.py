@@ -251,3 +251,45 @@ def match_tail_numpy(X11, X21, p1_int, valid_proj, dist_thresh=0.1):
     valid = np.asarray(valid_proj, bool) & (dist < np.float32(dist_thresh))
     idx = p1_int[..., 0] + w * p1_int[..., 1]
     return idx.astype(np.int32), valid[:, :, None]
+
+
+def constrain_points_to_ray_numpy(img_size, Xs, K):
+    """geometry.py:273-302 + backproject :229-246 restated with numpy fp32 ops (MLX fp32 in the
+    reference; cannot be imported here).  img_size = (H, W); K 3x3 or (fx, fy, cx, cy)."""
+    Xs = np.asarray(Xs, np.float32)
+    K = np.asarray(K, np.float32)
+    fx, fy, cx, cy = (K[0, 0], K[1, 1], K[0, 2], K[1, 2]) if K.shape == (3, 3) else K
+    h, w = img_size
+    v, u = np.meshgrid(np.arange(h, dtype=np.float32), np.arange(w, dtype=np.float32), indexing="ij")
+    u = np.broadcast_to(u.reshape(1, -1, 1), Xs[..., 2:3].shape)
+    v = np.broadcast_to(v.reshape(1, -1, 1), Xs[..., 2:3].shape)
+    z = Xs[..., 2:3]
+    x = (u - np.float32(cx)) / np.float32(fx) * z
+    y = (v - np.float32(cy)) / np.float32(fy) * z
+    return np.concatenate([x, y, z], axis=-1)
+
+
+def add_factors_numpy(ii, jj, match_out, Q_conf, min_match_frac, is_reloc=False):
+    """FactorGraph.add_factors (global_opt.py:86-136) restated with numpy fp32: returns None when the
+    reference returns False, else the rows it appends
+    (ii, jj, idx_i2j, idx_j2i, valid_match_j, valid_match_i, Qj, Qi)."""
+    idx_i2j, idx_j2i, vmj, vmi, Qii, Qjj, Qji, Qij = [np.asarray(a) for a in match_out]
+    b = idx_i2j.shape[0]
+    bi = np.broadcast_to(np.arange(b)[:, None], idx_i2j.shape)
+    Qj = np.sqrt(Qii.astype(np.float32)[bi, idx_i2j] * Qji.astype(np.float32))
+    Qi = np.sqrt(Qjj.astype(np.float32)[bi, idx_j2i] * Qij.astype(np.float32))
+    valid_j = vmj.astype(bool) & (Qj > Q_conf)
+    valid_i = vmi.astype(bool) & (Qi > Q_conf)
+    nj = valid_j.shape[1] * valid_j.shape[2]
+    ni = valid_i.shape[1] * valid_i.shape[2]
+    fj = valid_j.astype(np.float32).sum(axis=(1, 2)) / nj
+    fi = valid_i.astype(np.float32).sum(axis=(1, 2)) / ni
+    ii_t, jj_t = np.asarray(ii, np.int32), np.asarray(jj, np.int32)
+    invalid = np.minimum(fj, fi) < min_match_frac
+    invalid = (~(ii_t == (jj_t - 1))) & invalid
+    if invalid.any() and is_reloc:
+        return None
+    keep = ~invalid
+    if keep.sum() == 0:
+        return None
+    return (ii_t[keep], jj_t[keep], idx_i2j[keep], idx_j2i[keep], vmj[keep], vmi[keep], Qj[keep], Qi[keep])
