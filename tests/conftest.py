@@ -30,3 +30,12 @@ def oracle():
     from oracle import oracle as orc
     orc.build()
     return orc
+
+
+@pytest.fixture(autouse=True)
+def _default_config():
+    """every test starts from (and leaves behind) the default hot-path configuration"""
+    from mast3r_slam_b200 import config
+    config.set_config({})
+    yield
+    config.set_config({})
