@@ -143,6 +143,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--gn-iters", type=int, default=5)
+    ap.add_argument("--gn-precision", default="both", choices=["both", "mixed", "f64"],
+                    help="per-point arithmetic of the GN accumulate pass (include/m3s.h); 'both' "
+                         "reports the default (mixed) as `gn` and the fp64 pass as `gn_f64`")
     ap.add_argument("--desc", default="dyadic")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -277,7 +280,14 @@ def main():
     # ---- GN leg: 200-KF graph, edges sharded over ranks ------------------------------------------
     gn = None
     if not args.no_gn:
-        gn = gn_leg(args, rank, world, dev, peak)
+        first = "f64" if args.gn_precision == "f64" else "mixed"
+        gn = gn_leg(args, rank, world, dev, peak, first)
+        if args.gn_precision == "both":
+            f64 = gn_leg(args, rank, world, dev, peak, "f64")
+            gn["pose_diff_vs_f64"] = float((gn.pop("_poses") - f64.pop("_poses")).abs().max())
+            gn["gn_f64"] = {k: f64[k] for k in ("value", "ms_per_iter", "accumulate_ms",
+                                                "solve_update_ms", "roofline", "status", "precision")}
+        gn.pop("_poses", None)
 
     if rank == 0:
         line = {
@@ -300,7 +310,7 @@ def main():
         torch.distributed.destroy_process_group()
 
 
-def gn_leg(args, rank, world, dev, peak):
+def gn_leg(args, rank, world, dev, peak, precision):
     """Config 5: gauss_newton_points on a 200-KF / 1000-directed-edge graph, N = 196 608."""
     import ctypes as C
     import torch
@@ -310,7 +320,8 @@ def gn_leg(args, rank, world, dev, peak):
     g = synth.make_graph_torch(dev, 0, GN_KF, GN_LOOPS, H, W, edge_range=(eb, ee))
     assert len(g["ii"]) == e_total
     sg = mdist.ShardedGaussNewton(g["ii"], g["jj"], GN_KF, NPIX, 1, dev, eb, ee)
-    params = kernels.make_params(_lib.GN_POINTS, args.gn_iters, 1, 0.0, 0.0, 1.5, 0.01)
+    params = kernels.make_params(_lib.GN_POINTS, args.gn_iters, 1, 0.0, 0.0, 1.5, 0.01,
+                                 precision=precision)
     Twc = torch.from_numpy(g["Twc"]).to(dev)
     lib = _lib.load()
     stream = torch.cuda.current_stream(dev)
@@ -336,6 +347,9 @@ def gn_leg(args, rank, world, dev, peak):
     torch.cuda.synchronize()
     ms = mdist.max_over_ranks(e0.elapsed_time(e1), dev) / args.gn_iters
     status = sg.plan.status()
+    poses_after = torch.empty_like(Twc)
+    _lib.check(lib.m3s_gn_get_poses(sg.plan.handle, C.c_void_p(poses_after.data_ptr()), st))
+    torch.cuda.synchronize()
     # accumulate kernel alone (dominant): event-timed on its stream
     a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     reset()
@@ -361,7 +375,10 @@ def gn_leg(args, rank, world, dev, peak):
         "n_gpus": world, "scaling": "strong (edges sharded, 1 all-reduce of packed H,g per iteration)",
         "edges_this_rank": ne, "dim": sg.plan.dim,
         "accumulate_ms": round(acc_ms, 4), "solve_update_ms": round(ms - acc_ms, 4),
-        "roofline": {"bound": "hbm", "kernel": "gn_accum_kernel", "alg_bytes_per_launch": alg,
+        "precision": precision, "_poses": poses_after.double().cpu(),
+        "roofline": {"bound": "hbm",
+                     "kernel": "gn_accum_mixed_kernel" if precision == "mixed" else "gn_accum_kernel",
+                     "alg_bytes_per_launch": alg,
                      "achieved": round(alg / (acc_ms * 1e-3) / 1e9, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(alg / (acc_ms * 1e-3) / 1e9 / peak, 4)},
         "status": status,

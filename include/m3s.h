@@ -128,6 +128,18 @@ int m3s_edge_confidence(const float* Qii, const float* Qji, const int32_t* idx,
 
 /* ---- Gauss-Newton -------------------------------------------------------------------------- */
 
+/* Per-point arithmetic of m3s_gn_accumulate.
+ *   F64:   every per-point quantity in fp64, as the reference's numpy path (gauss_newton.py:92-220).
+ *   MIXED: per-point residual / Jacobian products in fp32 (what the reference's own GPU kernel does,
+ *          gauss_newton.metal:66-252), with the relative pose split into fp32 hi + lo parts so the
+ *          residual keeps its systematic accuracy; per-thread fp32 partial sums over <= 32 points,
+ *          everything above that in fp64.  Rounding errors are zero-mean per point and average out:
+ *          pose updates agree with the fp64 path to ~1e-8 relative (bar: 1e-5, tests/test_gpu_gn.py).
+ *   DEFAULT: MIXED unless the environment says M3S_GN_PRECISION=f64. */
+#define M3S_GN_PREC_DEFAULT 0
+#define M3S_GN_PREC_F64 1
+#define M3S_GN_PREC_MIXED 2
+
 /* Scalars of gauss_newton_{rays,points,calib} (backends/mpsgraph/kernels.py:262-279, 325-346,
  * 396-412).  sigma_a = sigma_ray | sigma_point | sigma_pixel; sigma_b = sigma_depth (calib). */
 typedef struct m3s_gn_params {
@@ -141,6 +153,9 @@ typedef struct m3s_gn_params {
     double delta_thresh;
     double z_eps;         /* calib */
     float K4[4];          /* calib: fx, fy, cx, cy (the reference passes K as fp32) */
+    int32_t precision;    /* M3S_GN_PREC_*: arithmetic of the per-point pass (reductions, H, the
+                             solve and the poses are fp64 in every mode) */
+    int32_t reserved;
 } m3s_gn_params;
 
 /* Per-graph plan: the free-keyframe numbering of gauss_newton.py:70-78 (sorted unique(ii U jj),

@@ -14,6 +14,7 @@ SO_PATH = os.environ.get("M3S_LIB") or os.path.join(_PKG, "libm3s_b200.so")
 
 GN_RAYS, GN_POINTS, GN_CALIB = 0, 1, 2
 GN_EDGE_STRIDE = 36
+GN_PREC_DEFAULT, GN_PREC_F64, GN_PREC_MIXED = 0, 1, 2
 
 
 class GNParams(C.Structure):
@@ -23,7 +24,7 @@ class GNParams(C.Structure):
         ("pixel_border", C.c_int32), ("img_w", C.c_int32), ("img_h", C.c_int32),
         ("sigma_a", C.c_double), ("sigma_b", C.c_double), ("C_thresh", C.c_double),
         ("Q_thresh", C.c_double), ("delta_thresh", C.c_double), ("z_eps", C.c_double),
-        ("K4", C.c_float * 4),
+        ("K4", C.c_float * 4), ("precision", C.c_int32), ("reserved", C.c_int32),
     ]
 
 

@@ -12,6 +12,9 @@
 // per-point work accumulates S = sum J'^T W J' and v = sum J'^T W err in the pose-free basis (29
 // sums for rays/points thanks to the sparsity of J', 35 for calib); the edge block is
 // A = G^T S G, b = G^T v, and  H_ii += A, H_jj += A, H_ij -= A, H_ji -= A, g_i -= b, g_j += b.
+#include <stdlib.h>
+#include <string.h>
+
 #include <algorithm>
 #include <map>
 #include <new>
@@ -317,6 +320,269 @@ gn_accum_kernel(const Status* __restrict__ status, KernelParams P, const double*
 #pragma unroll
         for (int w = 0; w < kAccThreads / 32; ++w) s += red[w][threadIdx.x];
         out[threadIdx.x] = s;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3 (mixed precision, M3S_GN_PREC_MIXED): the same sums with the per-point arithmetic in fp32.
+//
+// What has to stay accurate is the *systematic* part of the residual e = T_ij Xj - Xi: the relative
+// pose (s_ij R_ij, t_ij) is computed in fp64 and split into fp32 hi + lo parts, X' = hi-chain (3
+// FMA) and e = (X'_hi - Xi) + lo-chain; the first difference is exact when the residual is small
+// (Sterbenz), so e carries only the zero-mean rounding error of the hi chain (~2^-24 |X| per point).
+// Zero-mean per-point errors average out over the ~1e5 points of an edge: the resulting pose
+// perturbation is ~|e_round| / (sqrt(n) |J|) ~ 1e-9, three orders below the parity bar.  The same
+// holds for the fp32 weights, Jacobian products and the per-thread fp32 partial sums (<= 32
+// points); from the thread boundary upwards everything is fp64 with a fixed summation order.
+//
+// fp32 accumulators (29 / 35 registers instead of 58 / 70) also double the occupancy, and the block
+// reduction goes through shared memory (one transposed pass) instead of 29 x 5 64-bit shuffles.
+// ------------------------------------------------------------------------------------------------
+struct EdgeConstF {
+    float Rh[9], Rl[9];   // s_ij R_ij = Rh + Rl
+    float th[3], tl[3];   // t_ij = th + tl
+    float s_inv;          // 1 / s_i (Jacobian scale only)
+};
+
+constexpr float kHuberF = 1.345f;
+
+template <int MODE>
+__device__ __forceinline__ void accumulate_point_f32(const KernelParams& P, const EdgeConstF& ec,
+                                                     float X0, float X1, float X2, float xix,
+                                                     float xiy, float xiz, float qc, float* acc) {
+    const float x = fmaf(ec.Rh[0], X0, fmaf(ec.Rh[1], X1, fmaf(ec.Rh[2], X2, ec.th[0])));
+    const float y = fmaf(ec.Rh[3], X0, fmaf(ec.Rh[4], X1, fmaf(ec.Rh[5], X2, ec.th[1])));
+    const float z = fmaf(ec.Rh[6], X0, fmaf(ec.Rh[7], X1, fmaf(ec.Rh[8], X2, ec.th[2])));
+    const float xl = fmaf(ec.Rl[0], X0, fmaf(ec.Rl[1], X1, fmaf(ec.Rl[2], X2, ec.tl[0])));
+    const float yl = fmaf(ec.Rl[3], X0, fmaf(ec.Rl[4], X1, fmaf(ec.Rl[5], X2, ec.tl[1])));
+    const float zl = fmaf(ec.Rl[6], X0, fmaf(ec.Rl[7], X1, fmaf(ec.Rl[8], X2, ec.tl[2])));
+    if (MODE == M3S_GN_CALIB) {
+        const float zf = z + zl;
+        if (!(zf > (float)P.z_eps) || !(xiz > (float)P.z_eps)) return;
+        const float zinv = __fdividef(1.0f, zf);
+        const float zinv_i = __fdividef(1.0f, xiz);
+        const float xf = x + xl, yf = y + yl;
+        const float pju = fmaf(P.fx * xf, zinv, P.cx);
+        const float pjv = fmaf(P.fy * yf, zinv, P.cy);
+        if (!(pju >= (float)P.u_lo && pju < (float)P.u_hi && pjv >= (float)P.v_lo && pjv < (float)P.v_hi))
+            return;
+        // u_j - u_i = fx (x'/z' - xi/zi): the difference of the two ratios is formed before the
+        // multiplication by fx, so the pixel-scale rounding (2^-24 * 512) never enters
+        const float du = fmaf(xf, zinv, -xix * zinv_i) + 0.0f;
+        const float dv = fmaf(yf, zinv, -xiy * zinv_i) + 0.0f;
+        const float spx = (float)P.sig_px_inv, spz = (float)P.sig_z_inv;
+        const float e0 = P.fx * du * spx;
+        const float e1 = P.fy * dv * spx;
+        // ln z' - ln z_i = log1p((z' - z_i) / z_i): keeps the relative accuracy of the small difference
+        const float e2 = log1pf(((z - xiz) + zl) * zinv_i) * spz;
+        const float sw = sqrtf(qc);
+        const float w2 = sw * sw;
+        const float zinv2 = zinv * zinv;
+        const float pa = P.fx * zinv * spx;
+        const float pb = -P.fx * xf * zinv2 * spx;
+        const float pc = P.fy * zinv * spx;
+        const float pd = -P.fy * yf * zinv2 * spx;
+        const float pe = zinv * spz;
+        const float si = ec.s_inv;
+        const float J[3][7] = {
+            {pa * si, 0.0f, pb * si, pb * yf, pa * zf - pb * xf, -pa * yf, pa * xf + pb * zf},
+            {0.0f, pc * si, pd * si, -pc * zf + pd * yf, -pd * xf, pc * xf, pc * yf + pd * zf},
+            {0.0f, 0.0f, pe * si, pe * yf, -pe * xf, 0.0f, pe * zf}};
+        const float err[3] = {e0, e1, e2};
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float ra = fabsf(sw * err[c]);
+            const float w = (ra < kHuberF) ? w2 : __fdividef(kHuberF * w2, ra);
+            int k = 0;
+#pragma unroll
+            for (int a = 0; a < 7; ++a) {
+                const float wj = w * J[c][a];
+#pragma unroll
+                for (int b = a; b < 7; ++b) {
+                    // structural zeros of J' are skipped at compile time (their slots stay 0)
+                    const bool za = (c == 0 && a == 1) || (c == 1 && a == 0) || (c == 2 && (a == 0 || a == 1 || a == 5));
+                    const bool zb = (c == 0 && b == 1) || (c == 1 && b == 0) || (c == 2 && (b == 0 || b == 1 || b == 5));
+                    if (!za && !zb) acc[k] = fmaf(wj, J[c][b], acc[k]);
+                    ++k;
+                }
+                acc[28 + a] = fmaf(wj, err[c], acc[28 + a]);
+            }
+        }
+    } else {
+        const float e0 = (x - xix) + xl, e1 = (y - xiy) + yl, e2 = (z - xiz) + zl;
+        float sw = P.sig_inv_f * sqrtf(qc);
+        if (MODE == M3S_GN_POINTS) {
+            const float dist = sqrtf(fmaf(xix, xix, fmaf(xiy, xiy, xiz * xiz))) + 1e-6f;
+            sw = __fdividef(sw, dist);
+        }
+        const float w2 = sw * sw;
+        const float r0 = fabsf(sw * e0), r1 = fabsf(sw * e1), r2 = fabsf(sw * e2);
+        const float hw = kHuberF * w2;
+        const float w0 = (r0 < kHuberF) ? w2 : __fdividef(hw, r0);
+        const float w1 = (r1 < kHuberF) ? w2 : __fdividef(hw, r1);
+        const float w2c = (r2 < kHuberF) ? w2 : __fdividef(hw, r2);
+        const float w0y = w0 * y, w0z = w0 * z, w1x = w1 * x, w1z = w1 * z, w2x = w2c * x, w2y = w2c * y;
+        const float w0x = w0 * x, w1y = w1 * y, w2z = w2c * z;
+        acc[0] += w0; acc[1] += w1; acc[2] += w2c;
+        acc[3] += w0z; acc[4] += w0y; acc[5] += w1z; acc[6] += w1x; acc[7] += w2y; acc[8] += w2x;
+        acc[9] += w0x; acc[10] += w1y; acc[11] += w2z;
+        acc[12] = fmaf(w1z, z, fmaf(w2y, y, acc[12]));
+        acc[13] = fmaf(w0z, z, fmaf(w2x, x, acc[13]));
+        acc[14] = fmaf(w0y, y, fmaf(w1x, x, acc[14]));
+        acc[15] = fmaf(w2x, y, acc[15]);
+        acc[16] = fmaf(w1x, z, acc[16]);
+        acc[17] = fmaf(w0y, z, acc[17]);
+        acc[18] = fmaf(w2y - w1y, z, acc[18]);
+        acc[19] = fmaf(w0x - w2x, z, acc[19]);
+        acc[20] = fmaf(w1x - w0x, y, acc[20]);
+        acc[21] = fmaf(w0x, x, fmaf(w1y, y, fmaf(w2z, z, acc[21])));
+        const float u0 = w0 * e0, u1 = w1 * e1, u2 = w2c * e2;
+        acc[22] += u0; acc[23] += u1; acc[24] += u2;
+        acc[25] += fmaf(y, u2, -z * u1);
+        acc[26] += fmaf(z, u0, -x * u2);
+        acc[27] += fmaf(x, u1, -y * u0);
+        acc[28] = fmaf(x, u0, fmaf(y, u1, fmaf(z, u2, acc[28])));
+    }
+}
+
+#ifndef M3S_ACCF_MINBLOCKS
+#define M3S_ACCF_MINBLOCKS 3
+#endif
+
+template <int MODE>
+__global__ void __launch_bounds__(kAccThreads, M3S_ACCF_MINBLOCKS)
+gn_accum_mixed_kernel(const Status* __restrict__ status, KernelParams P,
+                      const double* __restrict__ poses, const EdgeMeta* __restrict__ meta,
+                      const float* __restrict__ Xs, const float* __restrict__ Cs,
+                      const int32_t* __restrict__ idx, const uint8_t* __restrict__ valid,
+                      const float* __restrict__ Q, long long N, int edge_begin, int nchunks,
+                      long long chunk_pts, int vec_ok, double* __restrict__ partials) {
+    if (status->stopped | status->failed) return;
+    constexpr int NA = AccCount<MODE>::value;
+    const int e = edge_begin + blockIdx.x / nchunks;
+    const int chunk = blockIdx.x % nchunks;
+    const EdgeMeta em = meta[e];
+    double* out = partials + ((size_t)e * nchunks + chunk) * kEdgeStride;
+    if (!em.active) return;
+
+    __shared__ EdgeConstF ec_s;
+    __shared__ float red[NA][kAccThreads];
+    if (threadIdx.x == 0) {
+        // sim3_relative (sim3_ops.py:96-126) in fp64, then split
+        const double* Ti = poses + 8 * em.ix;
+        const double* Tj = poses + 8 * em.jx;
+        const double si_inv = 1.0 / Ti[7];
+        const double sij = si_inv * Tj[7];
+        const double qi_inv[4] = {-Ti[3], -Ti[4], -Ti[5], Ti[6]};
+        double qij[4], R[9], Ri[9];
+        quat_mul(qi_inv, Tj + 3, qij);
+        quat_to_mat(qij, R);
+        quat_to_mat(qi_inv, Ri);
+        const double d0 = Tj[0] - Ti[0], d1 = Tj[1] - Ti[1], d2 = Tj[2] - Ti[2];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+            const double v = R[k] * sij;
+            const float h = (float)v;
+            ec_s.Rh[k] = h;
+            ec_s.Rl[k] = (float)(v - (double)h);
+        }
+        const double t[3] = {(Ri[0] * d0 + Ri[1] * d1 + Ri[2] * d2) * si_inv,
+                             (Ri[3] * d0 + Ri[4] * d1 + Ri[5] * d2) * si_inv,
+                             (Ri[6] * d0 + Ri[7] * d1 + Ri[8] * d2) * si_inv};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float h = (float)t[k];
+            ec_s.th[k] = h;
+            ec_s.tl[k] = (float)(t[k] - (double)h);
+        }
+        ec_s.s_inv = (float)si_inv;
+    }
+    __syncthreads();
+    const EdgeConstF& ec = ec_s;
+
+    float acc[NA];
+#pragma unroll
+    for (int k = 0; k < NA; ++k) acc[k] = 0.0f;
+
+    const float* __restrict__ Xi = Xs + (size_t)em.ix * N * 3;
+    const float* __restrict__ Ci = Cs + (size_t)em.ix * N;
+    const float* __restrict__ Xj = Xs + (size_t)em.jx * N * 3;
+    const float* __restrict__ Cj = Cs + (size_t)em.jx * N;
+    const int32_t* __restrict__ ide = idx + (size_t)e * N;
+    const uint8_t* __restrict__ ve = valid + (size_t)e * N;
+    const float* __restrict__ Qe = Q + (size_t)e * N;
+
+    const long long n0 = (long long)chunk * chunk_pts;
+    const long long n1 = min(N, n0 + chunk_pts);
+    if (vec_ok) {
+        const uchar4* __restrict__ v4p = reinterpret_cast<const uchar4*>(ve);
+        const float4* __restrict__ q4p = reinterpret_cast<const float4*>(Qe);
+        const int4* __restrict__ i4p = reinterpret_cast<const int4*>(ide);
+        const float4* __restrict__ c4p = reinterpret_cast<const float4*>(Cj);
+        const float4* __restrict__ x4p = reinterpret_cast<const float4*>(Xj);
+        const int Ni = (int)N;  // vec path is only taken for N < 2^31 (host check)
+        for (int g = (int)(n0 >> 2) + threadIdx.x; g < (int)(n1 >> 2); g += kAccThreads) {
+            const uchar4 v4 = __ldg(v4p + g);
+            const float4 q4 = __ldg(q4p + g);
+            const int4 i4 = __ldg(i4p + g);
+            const float4 c4 = __ldg(c4p + g);
+            const float4 xa = __ldg(x4p + 3 * g), xb = __ldg(x4p + 3 * g + 1), xc = __ldg(x4p + 3 * g + 2);
+            const unsigned char vv[4] = {v4.x, v4.y, v4.z, v4.w};
+            const float qq[4] = {q4.x, q4.y, q4.z, q4.w};
+            const int ii4[4] = {i4.x, i4.y, i4.z, i4.w};
+            const float cc[4] = {c4.x, c4.y, c4.z, c4.w};
+            const float xj[4][3] = {{xa.x, xa.y, xa.z}, {xa.w, xb.x, xb.y}, {xb.z, xb.w, xc.x}, {xc.y, xc.z, xc.w}};
+            bool okp[4];
+            float ci[4], xi[4][3];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                int m = ii4[u];
+                m += (m < 0) ? Ni : 0;  // numpy negative indexing (gauss_newton.py:125)
+                okp[u] = vv[u] && ((unsigned)m < (unsigned)Ni) && (qq[u] > P.q_th) && (cc[u] > P.c_th);
+                m = okp[u] ? m : 0;
+                ci[u] = __ldg(Ci + m);
+                const float* __restrict__ xp = Xi + 3 * (size_t)(unsigned)m;
+                xi[u][0] = __ldg(xp); xi[u][1] = __ldg(xp + 1); xi[u][2] = __ldg(xp + 2);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (okp[u] && (ci[u] > P.c_th))
+                    accumulate_point_f32<MODE>(P, ec, xj[u][0], xj[u][1], xj[u][2], xi[u][0], xi[u][1],
+                                               xi[u][2], qq[u], acc);
+            }
+        }
+    } else {
+        for (long long n = n0 + threadIdx.x; n < n1; n += kAccThreads) {
+            if (!__ldg(ve + n)) continue;
+            const float qc = __ldg(Qe + n);
+            long long m = __ldg(ide + n);
+            if (m < 0) m += N;
+            if (m < 0 || m >= N) continue;
+            if (!(qc > P.q_th) || !(__ldg(Cj + n) > P.c_th) || !(__ldg(Ci + m) > P.c_th)) continue;
+            accumulate_point_f32<MODE>(P, ec, __ldg(Xj + 3 * n), __ldg(Xj + 3 * n + 1), __ldg(Xj + 3 * n + 2),
+                                       __ldg(Xi + 3 * m), __ldg(Xi + 3 * m + 1), __ldg(Xi + 3 * m + 2),
+                                       qc, acc);
+        }
+    }
+    // block reduction in fp64 through one transposed shared-memory pass: thread (k, part) sums 32
+    // of the 256 per-thread partials of accumulator k (rotated start: conflict-free), the 8 parts
+    // are combined by a 3-step shuffle.  Fixed order => bitwise reproducible.
+#pragma unroll
+    for (int k = 0; k < NA; ++k) red[k][threadIdx.x] = acc[k];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    constexpr int PASSES = (NA * 8 + kAccThreads - 1) / kAccThreads;
+#pragma unroll
+    for (int ps = 0; ps < PASSES; ++ps) {
+        const int id = ps * kAccThreads + threadIdx.x;
+        const int k = min(id >> 3, NA - 1), part = id & 7;
+        double s = 0.0;
+#pragma unroll 8
+        for (int i = 0; i < 32; ++i) s += (double)red[k][part * 32 + ((i + lane) & 31)];
+        s += __shfl_down_sync(0xffffffffu, s, 4);
+        s += __shfl_down_sync(0xffffffffu, s, 2);
+        s += __shfl_down_sync(0xffffffffu, s, 1);
+        if (part == 0 && (id >> 3) < NA) out[id >> 3] = s;
     }
 }
 
@@ -977,6 +1243,16 @@ M3S_API int m3s_gn_get_poses(m3s_gn_plan* plan, float* Twc_out, m3s_stream_t str
     return launch_ok("gn_poses_f64_to_f32");
 }
 
+// M3S_GN_PREC_DEFAULT -> MIXED unless M3S_GN_PRECISION=f64 (read once)
+static int resolve_precision(int requested) {
+    if (requested == M3S_GN_PREC_F64 || requested == M3S_GN_PREC_MIXED) return requested;
+    static const int env_default = [] {
+        const char* v = getenv("M3S_GN_PRECISION");
+        return (v && (!strcmp(v, "f64") || !strcmp(v, "F64"))) ? M3S_GN_PREC_F64 : M3S_GN_PREC_MIXED;
+    }();
+    return env_default;
+}
+
 static KernelParams make_kernel_params(const m3s_gn_params* gp) {
     KernelParams P{};
     P.mode = gp->mode;
@@ -1000,6 +1276,7 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
                               const float* Q, int edge_begin, int edge_end, m3s_stream_t stream) {
     M3S_REQUIRE(plan && gp, "gn_accumulate: null pointer");
     M3S_REQUIRE(gp->mode >= 0 && gp->mode <= 2, "gn_accumulate: bad mode");
+    M3S_REQUIRE(gp->precision >= 0 && gp->precision <= 2, "gn_accumulate: bad precision");
     M3S_REQUIRE(edge_begin >= 0 && edge_end <= plan->E && edge_begin <= edge_end, "gn_accumulate: bad edge range");
     if (plan->F == 0 || plan->E == 0) return M3S_OK;
     M3S_REQUIRE(Xs && Cs && idx && valid && Q, "gn_accumulate: null pointer");
@@ -1017,9 +1294,23 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
                                                         Xs, Cs, idx, valid, Q, plan->N,          \
                                                         edge_begin, plan->nchunks,               \
                                                         plan->chunk_pts, vec_ok, plan->partials)
-        if (gp->mode == M3S_GN_RAYS) M3S_ACC(M3S_GN_RAYS);
-        else if (gp->mode == M3S_GN_POINTS) M3S_ACC(M3S_GN_POINTS);
-        else M3S_ACC(M3S_GN_CALIB);
+#define M3S_ACCF(MODE)                                                                          \
+    gn_accum_mixed_kernel<MODE><<<grid, kAccThreads, 0, st>>>(plan->status, P, plan->poses,      \
+                                                              plan->meta, Xs, Cs, idx, valid, Q, \
+                                                              plan->N, edge_begin, plan->nchunks, \
+                                                              plan->chunk_pts,                   \
+                                                              vec_ok && plan->N < (1LL << 29),   \
+                                                              plan->partials)
+        if (resolve_precision(gp->precision) == M3S_GN_PREC_MIXED) {
+            if (gp->mode == M3S_GN_RAYS) M3S_ACCF(M3S_GN_RAYS);
+            else if (gp->mode == M3S_GN_POINTS) M3S_ACCF(M3S_GN_POINTS);
+            else M3S_ACCF(M3S_GN_CALIB);
+        } else {
+            if (gp->mode == M3S_GN_RAYS) M3S_ACC(M3S_GN_RAYS);
+            else if (gp->mode == M3S_GN_POINTS) M3S_ACC(M3S_GN_POINTS);
+            else M3S_ACC(M3S_GN_CALIB);
+        }
+#undef M3S_ACCF
 #undef M3S_ACC
         if (int rc = launch_ok("gn_accum_kernel")) return rc;
     }

@@ -349,9 +349,27 @@ def get_plan(ii, jj, num_kf, num_pts, pin, device) -> GNPlan:
     return plan
 
 
+_gn_precision = None  # None = library default (mixed unless M3S_GN_PRECISION=f64)
+
+
+def set_gn_precision(precision):
+    """Per-point arithmetic of the Gauss-Newton accumulate pass for every later call that does not
+    name one itself: None (library default), "f64" (the reference's numpy arithmetic) or "mixed"
+    (fp32 per-point products, fp64 reductions / H / solve / poses); see include/m3s.h."""
+    global _gn_precision
+    if precision not in (None, "default", "f64", "mixed"):
+        raise ValueError(f"unknown GN precision {precision!r}")
+    _gn_precision = None if precision == "default" else precision
+
+
 def make_params(mode, max_iter, pin, delta_thresh, C_thresh, Q_thresh, sigma_a, sigma_b=1.0,
-                K=None, img_size=(0, 0), pixel_border=0, z_eps=0.0) -> GNParams:
+                K=None, img_size=(0, 0), pixel_border=0, z_eps=0.0, precision=None) -> GNParams:
+    """``precision``: None / "default", "f64" or "mixed" (include/m3s.h, M3S_GN_PREC_*)."""
     p = GNParams()
+    if precision is None:
+        precision = _gn_precision
+    p.precision = {None: _lib.GN_PREC_DEFAULT, "default": _lib.GN_PREC_DEFAULT,
+                   "f64": _lib.GN_PREC_F64, "mixed": _lib.GN_PREC_MIXED}[precision]
     p.mode, p.max_iter, p.pin = int(mode), int(max_iter), int(pin)
     p.pixel_border, p.img_w, p.img_h = int(pixel_border), int(img_size[0]), int(img_size[1])
     p.sigma_a, p.sigma_b = float(sigma_a), float(sigma_b)

@@ -21,6 +21,15 @@ def K():
     return kernels
 
 
+@pytest.fixture(autouse=True, params=["f64", "mixed"])
+def precision(request, K):
+    """every test runs with both per-point arithmetics of the accumulate pass (include/m3s.h,
+    M3S_GN_PREC_*); the 1e-5 bar on the pose update is the same for both"""
+    K.set_gn_precision(request.param)
+    yield request.param
+    K.set_gn_precision(None)
+
+
 @pytest.fixture(scope="module")
 def synth():
     from mast3r_slam_b200 import synth as s
@@ -93,7 +102,7 @@ def test_gn_early_outs(K, golden):
 
 
 @pytest.mark.parametrize("mode", ["rays", "points", "calib"])
-def test_gn_first_iteration_internals(K, oracle, synth, mode):
+def test_gn_first_iteration_internals(K, oracle, synth, mode, precision):
     """H, g (fp64) and dx of iteration 1 against the oracle's, through the step-wise C ABI"""
     import ctypes as C
     import torch
@@ -127,12 +136,15 @@ def test_gn_first_iteration_internals(K, oracle, synth, mode):
     gv = plan.g().cpu().numpy()
     assert plan.F == dbg["F"] and H.shape == dbg["H"].shape
     scale = np.abs(dbg["H"]).max()
-    assert np.abs(H - dbg["H"]).max() <= 1e-11 * scale
-    assert np.abs(gv - dbg["g"]).max() <= 1e-11 * np.abs(dbg["g"]).max()
+    # fp64 per-point arithmetic: round-off of a different summation order only; mixed: zero-mean
+    # fp32 rounding of ~2000 terms per edge
+    tol_h, tol_g, tol_dx = (1e-11, 1e-11, 1e-7) if precision == "f64" else (2e-6, 2e-6, 2e-5)
+    assert np.abs(H - dbg["H"]).max() <= tol_h * scale
+    assert np.abs(gv - dbg["g"]).max() <= tol_g * np.abs(dbg["g"]).max()
     _lib.check(lib.m3s_gn_solve_update(plan.handle, C.byref(params), None))
     torch.cuda.synchronize()
     dx = plan.dx().cpu().numpy()
-    assert np.abs(dx - dbg["dx"][0]).max() <= 1e-7 * np.abs(dbg["dx"][0]).max()
+    assert np.abs(dx - dbg["dx"][0]).max() <= tol_dx * np.abs(dbg["dx"][0]).max()
     st = plan.status()
     assert st["applied"] == 1 and not st["failed"]
     out = torch.empty_like(Twc)
