@@ -133,8 +133,9 @@ int m3s_edge_confidence(const float* Qii, const float* Qji, const int32_t* idx,
  *   MIXED: per-point residual / Jacobian products in fp32 (what the reference's own GPU kernel does,
  *          gauss_newton.metal:66-252), with the relative pose split into fp32 hi + lo parts so the
  *          residual keeps its systematic accuracy; per-thread fp32 partial sums over <= 32 points,
- *          everything above that in fp64.  Rounding errors are zero-mean per point and average out:
- *          pose updates agree with the fp64 path to ~1e-8 relative (bar: 1e-5, tests/test_gpu_gn.py).
+ *          everything above that in fp64.  Pose updates agree with the fp64 pass to 1e-7..5e-7
+ *          relative (bar: 1e-5; scripts/gn_precision_report.py, tests/test_gpu_gn.py).  Rays and
+ *          points only: calib always runs the F64 pass (weakly constrained depth direction).
  *   DEFAULT: MIXED unless the environment says M3S_GN_PRECISION=f64. */
 #define M3S_GN_PREC_DEFAULT 0
 #define M3S_GN_PREC_F64 1
@@ -179,6 +180,8 @@ double* m3s_gn_plan_H(m3s_gn_plan* plan);   /* [dim rows, ld] f64 (device): H + 
                                                factor (lower) in m3s_gn_solve_update */
 double* m3s_gn_plan_g(m3s_gn_plan* plan);   /* [dim] */
 double* m3s_gn_plan_dx(m3s_gn_plan* plan);  /* [dim] last solved step */
+double* m3s_gn_plan_poses(m3s_gn_plan* plan); /* [num_kf, 8] f64: the solver's pose state
+                                                 (gauss_newton.py:92, Twc.astype(float64)) */
 
 /* Load poses Twc [num_kf,8] f32 (tx,ty,tz,qx,qy,qz,qw,s) into the plan's fp64 state
  * (gauss_newton.py:92-94) and reset the iteration status. */

@@ -346,6 +346,18 @@ struct EdgeConstF {
 
 constexpr float kHuberF = 1.345f;
 
+// MUFU.SQRT / MUFU.RCP without the IEEE fix-up sequences (~1 ulp; mixed mode only)
+__device__ __forceinline__ float sqrt_approx(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 template <int MODE>
 __device__ __forceinline__ void accumulate_point_f32(const KernelParams& P, const EdgeConstF& ec,
                                                      float X0, float X1, float X2, float xix,
@@ -356,71 +368,20 @@ __device__ __forceinline__ void accumulate_point_f32(const KernelParams& P, cons
     const float xl = fmaf(ec.Rl[0], X0, fmaf(ec.Rl[1], X1, fmaf(ec.Rl[2], X2, ec.tl[0])));
     const float yl = fmaf(ec.Rl[3], X0, fmaf(ec.Rl[4], X1, fmaf(ec.Rl[5], X2, ec.tl[1])));
     const float zl = fmaf(ec.Rl[6], X0, fmaf(ec.Rl[7], X1, fmaf(ec.Rl[8], X2, ec.tl[2])));
-    if (MODE == M3S_GN_CALIB) {
-        const float zf = z + zl;
-        if (!(zf > (float)P.z_eps) || !(xiz > (float)P.z_eps)) return;
-        const float zinv = __fdividef(1.0f, zf);
-        const float zinv_i = __fdividef(1.0f, xiz);
-        const float xf = x + xl, yf = y + yl;
-        const float pju = fmaf(P.fx * xf, zinv, P.cx);
-        const float pjv = fmaf(P.fy * yf, zinv, P.cy);
-        if (!(pju >= (float)P.u_lo && pju < (float)P.u_hi && pjv >= (float)P.v_lo && pjv < (float)P.v_hi))
-            return;
-        // u_j - u_i = fx (x'/z' - xi/zi): the difference of the two ratios is formed before the
-        // multiplication by fx, so the pixel-scale rounding (2^-24 * 512) never enters
-        const float du = fmaf(xf, zinv, -xix * zinv_i) + 0.0f;
-        const float dv = fmaf(yf, zinv, -xiy * zinv_i) + 0.0f;
-        const float spx = (float)P.sig_px_inv, spz = (float)P.sig_z_inv;
-        const float e0 = P.fx * du * spx;
-        const float e1 = P.fy * dv * spx;
-        // ln z' - ln z_i = log1p((z' - z_i) / z_i): keeps the relative accuracy of the small difference
-        const float e2 = log1pf(((z - xiz) + zl) * zinv_i) * spz;
-        const float sw = sqrtf(qc);
-        const float w2 = sw * sw;
-        const float zinv2 = zinv * zinv;
-        const float pa = P.fx * zinv * spx;
-        const float pb = -P.fx * xf * zinv2 * spx;
-        const float pc = P.fy * zinv * spx;
-        const float pd = -P.fy * yf * zinv2 * spx;
-        const float pe = zinv * spz;
-        const float si = ec.s_inv;
-        const float J[3][7] = {
-            {pa * si, 0.0f, pb * si, pb * yf, pa * zf - pb * xf, -pa * yf, pa * xf + pb * zf},
-            {0.0f, pc * si, pd * si, -pc * zf + pd * yf, -pd * xf, pc * xf, pc * yf + pd * zf},
-            {0.0f, 0.0f, pe * si, pe * yf, -pe * xf, 0.0f, pe * zf}};
-        const float err[3] = {e0, e1, e2};
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            const float ra = fabsf(sw * err[c]);
-            const float w = (ra < kHuberF) ? w2 : __fdividef(kHuberF * w2, ra);
-            int k = 0;
-#pragma unroll
-            for (int a = 0; a < 7; ++a) {
-                const float wj = w * J[c][a];
-#pragma unroll
-                for (int b = a; b < 7; ++b) {
-                    // structural zeros of J' are skipped at compile time (their slots stay 0)
-                    const bool za = (c == 0 && a == 1) || (c == 1 && a == 0) || (c == 2 && (a == 0 || a == 1 || a == 5));
-                    const bool zb = (c == 0 && b == 1) || (c == 1 && b == 0) || (c == 2 && (b == 0 || b == 1 || b == 5));
-                    if (!za && !zb) acc[k] = fmaf(wj, J[c][b], acc[k]);
-                    ++k;
-                }
-                acc[28 + a] = fmaf(wj, err[c], acc[28 + a]);
-            }
-        }
-    } else {
+    static_assert(MODE != M3S_GN_CALIB, "calib runs the fp64 pass (see m3s_gn_accumulate)");
+    {
         const float e0 = (x - xix) + xl, e1 = (y - xiy) + yl, e2 = (z - xiz) + zl;
-        float sw = P.sig_inv_f * sqrtf(qc);
+        float sw = P.sig_inv_f * sqrt_approx(qc);
         if (MODE == M3S_GN_POINTS) {
-            const float dist = sqrtf(fmaf(xix, xix, fmaf(xiy, xiy, xiz * xiz))) + 1e-6f;
-            sw = __fdividef(sw, dist);
+            const float dist = sqrt_approx(fmaf(xix, xix, fmaf(xiy, xiy, xiz * xiz))) + 1e-6f;
+            sw *= rcp_approx(dist);
         }
         const float w2 = sw * sw;
         const float r0 = fabsf(sw * e0), r1 = fabsf(sw * e1), r2 = fabsf(sw * e2);
         const float hw = kHuberF * w2;
-        const float w0 = (r0 < kHuberF) ? w2 : __fdividef(hw, r0);
-        const float w1 = (r1 < kHuberF) ? w2 : __fdividef(hw, r1);
-        const float w2c = (r2 < kHuberF) ? w2 : __fdividef(hw, r2);
+        const float w0 = (r0 < kHuberF) ? w2 : hw * rcp_approx(r0);
+        const float w1 = (r1 < kHuberF) ? w2 : hw * rcp_approx(r1);
+        const float w2c = (r2 < kHuberF) ? w2 : hw * rcp_approx(r2);
         const float w0y = w0 * y, w0z = w0 * z, w1x = w1 * x, w1z = w1 * z, w2x = w2c * x, w2y = w2c * y;
         const float w0x = w0 * x, w1y = w1 * y, w2z = w2c * z;
         acc[0] += w0; acc[1] += w1; acc[2] += w2c;
@@ -446,7 +407,7 @@ __device__ __forceinline__ void accumulate_point_f32(const KernelParams& P, cons
 }
 
 #ifndef M3S_ACCF_MINBLOCKS
-#define M3S_ACCF_MINBLOCKS 3
+#define M3S_ACCF_MINBLOCKS 2
 #endif
 
 template <int MODE>
@@ -498,7 +459,12 @@ gn_accum_mixed_kernel(const Status* __restrict__ status, KernelParams P,
         ec_s.s_inv = (float)si_inv;
     }
     __syncthreads();
+#ifdef M3S_ACCF_EC_SMEM
     const EdgeConstF& ec = ec_s;
+#else
+    const EdgeConstF ec = ec_s;  // 25 registers; re-reading them from shared memory every trip
+                                 // cost 25 LDS per 4 points (l1tex data pipe 67 % busy, ncu s10a)
+#endif
 
     float acc[NA];
 #pragma unroll
@@ -1226,6 +1192,7 @@ M3S_API double* m3s_gn_plan_edge_blocks(m3s_gn_plan* plan, int64_t* count_out) {
 M3S_API double* m3s_gn_plan_H(m3s_gn_plan* plan) { return plan ? plan->Hm : nullptr; }
 M3S_API double* m3s_gn_plan_g(m3s_gn_plan* plan) { return plan ? plan->g : nullptr; }
 M3S_API double* m3s_gn_plan_dx(m3s_gn_plan* plan) { return plan ? plan->dx : nullptr; }
+M3S_API double* m3s_gn_plan_poses(m3s_gn_plan* plan) { return plan ? plan->poses : nullptr; }
 
 M3S_API int m3s_gn_set_poses(m3s_gn_plan* plan, const float* Twc, m3s_stream_t stream) {
     M3S_REQUIRE(plan && Twc, "gn_set_poses: null pointer");
@@ -1301,10 +1268,13 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
                                                               plan->chunk_pts,                   \
                                                               vec_ok && plan->N < (1LL << 29),   \
                                                               plan->partials)
-        if (resolve_precision(gp->precision) == M3S_GN_PREC_MIXED) {
+        // calib always takes the fp64 pass: its depth direction is weakly constrained (sigma_depth),
+        // which amplifies the fp32 rounding of X' (4e-5 px) to a 1e-5 relative deviation of the
+        // update (scripts/gn_precision_report.py), and its problems are 2-keyframe tracking solves
+        // (config 4) where the pass takes microseconds either way
+        if (resolve_precision(gp->precision) == M3S_GN_PREC_MIXED && gp->mode != M3S_GN_CALIB) {
             if (gp->mode == M3S_GN_RAYS) M3S_ACCF(M3S_GN_RAYS);
-            else if (gp->mode == M3S_GN_POINTS) M3S_ACCF(M3S_GN_POINTS);
-            else M3S_ACCF(M3S_GN_CALIB);
+            else M3S_ACCF(M3S_GN_POINTS);
         } else {
             if (gp->mode == M3S_GN_RAYS) M3S_ACC(M3S_GN_RAYS);
             else if (gp->mode == M3S_GN_POINTS) M3S_ACC(M3S_GN_POINTS);

@@ -319,6 +319,10 @@ class GNPlan:
     def g(self) -> torch.Tensor:
         return self._view(self._lib.m3s_gn_plan_g(self.handle), self.dim)
 
+    def poses(self) -> torch.Tensor:
+        """[num_kf, 8] fp64 pose state of the solver (before the final float32 cast)."""
+        return self._view(self._lib.m3s_gn_plan_poses(self.handle), 8 * self.num_kf).view(-1, 8)
+
     def dx(self) -> torch.Tensor:
         return self._view(self._lib.m3s_gn_plan_dx(self.handle), self.dim)
 
