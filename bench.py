@@ -142,6 +142,7 @@ def main():
     ap.add_argument("--no-gn", action="store_true", help="skip the 200-keyframe Gauss-Newton leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--chunk-pairs", type=int, default=4, help="pairs per pipelined chunk (e2e leg)")
     ap.add_argument("--gn-iters", type=int, default=5)
     ap.add_argument("--gn-precision", default="both", choices=["both", "mixed", "f64"],
                     help="per-point arithmetic of the GN accumulate pass (include/m3s.h); 'both' "
@@ -172,6 +173,7 @@ def main():
     rays, pts, p0 = kernels.prep_for_iter_proj(pairs["X11"], pairs["X21"], None)
     D11 = pairs["D11"]
     D21 = pairs["D21"].reshape(B, NPIX, D)
+    X11, X21 = pairs["X11"], pairs["X21"]
     del pairs
     torch.cuda.synchronize()
 
@@ -233,38 +235,70 @@ def main():
                  "frac": round(path_gbs / peak, 4)},
     }
 
-    # ---- e2e: pinned host inputs -> H2D -> both kernels -> D2H of positions + validity -----------
+    # ---- e2e: the reference-facing call on HOST buffers -------------------------------------------
+    # matching.match_iterative_proj(X11, X21, D11, D21) (matching.py:339, the call mast3r_utils.py:490
+    # makes) with page-locked host inputs and outputs: per step H2D of the four inputs, prep +
+    # iter_proj + refine_matches + tail on the device, D2H of idx + valid, chunk-pipelined inside
+    # m3s_match_iterative_proj_host.  The call is synchronous, so it is timed with the host clock
+    # between device synchronisations.  `l1_unpipelined` = the same through the two L1 operator
+    # calls (rays / pts / p_init / D11 / D21 uploaded whole, one stream), for comparison.
     e2e = None
     host = None
     if not args.no_e2e:
-        hp = {k: torch.empty(t.shape, dtype=t.dtype, pin_memory=True).copy_(t)
-              for k, t in (("rays", rays), ("pts", pts), ("p0", p0), ("D11", D11), ("D21", D21))}
-        out_p1 = torch.empty((B, NPIX, 2), dtype=torch.int32, pin_memory=True)
-        out_v = torch.empty((B, NPIX), dtype=torch.bool, pin_memory=True)
-        h2d = sum(t.numel() * t.element_size() for t in hp.values())
-        d2h = out_p1.numel() * 4 + out_v.numel()
+        pin = lambda t: torch.empty(t.shape, dtype=t.dtype, pin_memory=True).copy_(t)  # noqa: E731
+        hX11, hX21, hD11, hD21 = pin(X11), pin(X21), pin(D11), pin(D21.reshape(B, H, W, D))
+        out_idx = torch.empty((B, NPIX), dtype=torch.int32, pin_memory=True)
+        out_val = torch.empty((B, NPIX), dtype=torch.uint8, pin_memory=True)
+        h2d = sum(t.numel() * t.element_size() for t in (hX11, hX21, hD11, hD21))
+        d2h = out_idx.numel() * 4 + out_val.numel()
 
         def step_e2e():
-            d = {k: t.to(dev, non_blocking=True) for k, t in hp.items()}
-            p, valid = kernels.iter_proj(d["rays"], d["pts"], d["p0"], MAX_ITER, LAMBDA, THRESH)
-            p1 = kernels.refine_matches(d["D11"], d["D21"], p, RADIUS, 0)
-            out_p1.copy_(p1, non_blocking=True)
-            out_v.copy_(valid, non_blocking=True)
+            kernels.match_iterative_proj_host(hX11, hX21, hD11, hD21, None, MAX_ITER, LAMBDA, THRESH,
+                                              RADIUS, 0, 0.1, chunk_pairs=args.chunk_pairs,
+                                              out=(out_idx, out_val), device=dev)
 
         e_steps = max(2, min(args.steps, 5))
         step_e2e()
         barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
+        t0 = time.perf_counter()
         for _ in range(e_steps):
             step_e2e()
-        e1.record(stream)
         torch.cuda.synchronize()
-        t_e2e_ms = mdist.max_over_ranks(e0.elapsed_time(e1), dev) / e_steps
+        t_e2e_ms = mdist.max_over_ranks(1e3 * (time.perf_counter() - t0), dev) / e_steps
         e2e = {"value": world * B * NPIX / (t_e2e_ms * 1e-3), "unit": "px/s",
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": round(t_e2e_ms, 3),
-               "steps": e_steps}
-        host = {k: v.numpy() for k, v in hp.items()}
+               "steps": e_steps, "api": "matching.match_iterative_proj on page-locked host arrays "
+               "(m3s_match_iterative_proj_host)", "chunk_pairs": args.chunk_pairs,
+               "timer": "host clock around the synchronous call, device synchronised on both sides",
+               "gpu_launches_per_step": 6 * ((B + args.chunk_pairs - 1) // args.chunk_pairs)}
+        # L1 operators, whole-batch upload on one stream
+        hp = {k: pin(t) for k, t in (("rays", rays), ("pts", pts), ("p0", p0))}
+        out_p1 = torch.empty((B, NPIX, 2), dtype=torch.int32, pin_memory=True)
+
+        def step_l1():
+            d = {k: t.to(dev, non_blocking=True) for k, t in hp.items()}
+            d11, d21 = hD11.to(dev, non_blocking=True), hD21.to(dev, non_blocking=True)
+            p, valid = kernels.iter_proj(d["rays"], d["pts"], d["p0"], MAX_ITER, LAMBDA, THRESH)
+            p1 = kernels.refine_matches(d11, d21.reshape(B, NPIX, D), p, RADIUS, 0)
+            out_p1.copy_(p1, non_blocking=True)
+            out_val.copy_(valid, non_blocking=True)
+
+        step_l1()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(2):
+            step_l1()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        t_l1 = mdist.max_over_ranks(e0.elapsed_time(e1), dev) / 2
+        e2e["l1_unpipelined"] = {
+            "value": world * B * NPIX / (t_l1 * 1e-3), "ms_per_step": round(t_l1, 3),
+            "h2d_bytes_per_step": h2d - hX11.numel() * 8 + sum(t.numel() * 4 for t in hp.values()),
+            "d2h_bytes_per_step": out_p1.numel() * 4 + out_val.numel()}
+        host = {"rays": hp["rays"].numpy(), "pts": hp["pts"].numpy(), "p0": hp["p0"].numpy(),
+                "D11": hD11.numpy(), "D21": hD21.numpy().reshape(B, NPIX, D)}
+        del hX11, hX21
 
     # ---- CPU baseline (rank 0, N = 1 only) -------------------------------------------------------
     cpu_baseline = None
@@ -273,7 +307,7 @@ def main():
             host = {k: t.cpu().numpy() for k, t in (("rays", rays), ("pts", pts), ("p0", p0), ("D11", D11), ("D21", D21))}
         v, cores, sample = cpu_oracle_rate(host)
         cpu_baseline = {"value": v, "unit": "px/s", "cores": cores, "kind": "port", "sample": sample}
-    del rays, pts, p0, D11, D21
+    del rays, pts, p0, D11, D21, X11, X21
     host = None
     torch.cuda.empty_cache()
 

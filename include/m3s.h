@@ -107,6 +107,22 @@ int m3s_match_iterative_proj(const float* X11, const float* X21, const float* D1
                              int dilation_max, float dist_thresh, void* workspace,
                              size_t workspace_bytes, m3s_stream_t stream);
 
+/* Same computation on HOST arrays (what the reference's caller holds: mast3r_utils.py:490 passes
+ * host arrays to matching.match): the batch is cut into chunks of `chunk_pairs` pairs (<= 0: 4)
+ * that are uploaded, matched and downloaded on three rotating streams, so the upload of chunk
+ * c+1 overlaps the kernels of chunk c and the download of chunk c-1.  Device buffers for one
+ * chunk per stream are kept between calls (m3s_match_host_release frees them).  Host pointers
+ * should be page-locked for the overlap; pageable memory is still correct.  `device` = CUDA
+ * ordinal.  SYNCHRONOUS: returns when idx_out_host / valid_out_host are complete. */
+int m3s_match_iterative_proj_host(const float* X11_host, const float* X21_host,
+                                  const float* D11_host, const float* D21_host,
+                                  const int32_t* idx_init_host, int32_t* idx_out_host,
+                                  uint8_t* valid_out_host, int B, int H, int W, int D,
+                                  int max_iter, float lambda_init, float convergence_thresh,
+                                  int radius, int dilation_max, float dist_thresh,
+                                  int chunk_pairs, int device);
+int m3s_match_host_release(int device);
+
 /* ---- factor-graph host steps (between match() and gauss_newton_*()) --------------------------- */
 
 /* Replaces constrain_points_to_ray (geometry.py:273-302) = backproject (geometry.py:229-246) of

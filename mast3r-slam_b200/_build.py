@@ -23,6 +23,7 @@ SOURCES = {
     "refine.cu": [],
     "gn.cu": [],
     "graph_host.cu": ["-fmad=false"],
+    "host_pipeline.cu": [],
 }
 
 

@@ -45,6 +45,9 @@ SIGNATURES = {
     "m3s_match_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "m3s_match_iterative_proj": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f,
                                       _f, _i, _i, _f, _vp, _sz, _vp]),
+    "m3s_match_iterative_proj_host": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f,
+                                           _f, _i, _i, _f, _i, _i]),
+    "m3s_match_host_release": (_i, [_i]),
     "m3s_constrain_points_to_ray": (_i, [_vp, C.POINTER(C.c_float), _vp, _i, _i, _i, _vp]),
     "m3s_edge_confidence": (_i, [_vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _i, C.c_longlong, _vp]),
     "m3s_gn_plan_create": (_vp, [_vp, _vp, _i, _i, _i64, _i, _i]),

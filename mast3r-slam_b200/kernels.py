@@ -25,7 +25,7 @@ from . import _lib
 from ._lib import GNParams, M3SError  # noqa: F401
 
 __all__ = ["is_available", "iter_proj", "refine_matches", "gauss_newton_rays",
-           "gauss_newton_points", "gauss_newton_calib", "match_iterative_proj_device",
+           "gauss_newton_points", "gauss_newton_calib", "match_iterative_proj_device", "match_iterative_proj_host",
            "prep_for_iter_proj", "match_tail", "GNPlan", "constrain_points_to_ray", "edge_confidence"]
 
 _workspaces: dict = {}
@@ -238,6 +238,9 @@ def match_iterative_proj_device(X11, X21, D11, D21, idx_init=None, max_iter=10, 
                                 convergence_thresh=1e-6, radius=3, dilation_max=2, dist_thresh=0.1):
     """Whole match_iterative_proj (matching.py:339-461) as ONE C-ABI call on device tensors.
     Returns (idx [B,N] i32, valid [B,N,1] bool) as CUDA tensors (or numpy when given numpy)."""
+    if not any(isinstance(x, torch.Tensor) and x.is_cuda for x in (X11, X21, D11, D21)):
+        return match_iterative_proj_host(X11, X21, D11, D21, idx_init, max_iter, lambda_init,
+                                         convergence_thresh, radius, dilation_max, dist_thresh)
     as_np = _wants_numpy(X11, X21, D11, D21)
     dev = _device(X11, X21, D11, D21)
     with torch.cuda.device(dev):
@@ -259,6 +262,66 @@ def match_iterative_proj_device(X11, X21, D11, D21, idx_init=None, max_iter=10, 
             ws.numel(), _stream(dev)), "match_iterative_proj")
         valid = valid.view(torch.bool)[:, :, None]
     return _out(idx, as_np), _out(valid, as_np)
+
+
+def _host_f32(x):
+    """host array -> (C-contiguous float32 numpy view, keep-alive object); no copy when possible"""
+    if isinstance(x, torch.Tensor):
+        t = x.detach().to(torch.float32).contiguous()
+        return t.numpy(), t
+    a = np.ascontiguousarray(np.asarray(x), dtype=np.float32)
+    return a, a
+
+
+def match_iterative_proj_host(X11, X21, D11, D21, idx_init=None, max_iter=10, lambda_init=1e-8,
+                              convergence_thresh=1e-6, radius=3, dilation_max=2, dist_thresh=0.1,
+                              chunk_pairs=4, out=None, device=None):
+    """match_iterative_proj (matching.py:339-461) on HOST arrays (numpy or CPU torch tensors, the
+    reference's calling convention) through the chunk-pipelined C-ABI entry point
+    m3s_match_iterative_proj_host: upload, kernels and download of consecutive chunks of
+    ``chunk_pairs`` pairs overlap on three streams.  Page-locked inputs (torch ``pin_memory``)
+    make the copies asynchronous; ``out = (idx int32 [B,N], valid uint8/bool [B,N])`` lets the
+    caller provide (page-locked) result arrays.  Returns (idx [B,N] i32, valid [B,N,1] bool) as
+    numpy arrays (CPU torch tensors when the inputs were torch tensors)."""
+    _lib.require_device()
+    as_torch = any(isinstance(x, torch.Tensor) for x in (X11, X21, D11, D21))
+    x11, k1 = _host_f32(X11)
+    x21, k2 = _host_f32(X21)
+    b, h, w, _ = x11.shape
+    use_desc = radius > 0
+    d11 = d21 = None
+    d = 0
+    if use_desc or D11 is not None:
+        d11, k3 = _host_f32(D11)
+        d21, k4 = _host_f32(D21)
+        d = d11.shape[-1]
+    init = None
+    if idx_init is not None:
+        init = (idx_init.detach().to(torch.int32).contiguous().numpy() if isinstance(idx_init, torch.Tensor)
+                else np.ascontiguousarray(np.asarray(idx_init), dtype=np.int32))
+    if out is not None:
+        idx_o, valid_o = out
+        idx_a = idx_o.numpy() if isinstance(idx_o, torch.Tensor) else idx_o
+        valid_a = valid_o.numpy() if isinstance(valid_o, torch.Tensor) else valid_o
+        if idx_a.dtype != np.int32 or valid_a.dtype not in (np.uint8, np.bool_) or \
+                idx_a.size != b * h * w or valid_a.size != b * h * w or \
+                not idx_a.flags.c_contiguous or not valid_a.flags.c_contiguous:
+            raise M3SError("match_iterative_proj_host: out must be C-contiguous (int32 [B,N], uint8/bool [B,N])")
+    else:
+        idx_a = np.empty((b, h * w), np.int32)
+        valid_a = np.empty((b, h * w), np.bool_)
+    dev_index = (torch.cuda.current_device() if device is None
+                 else torch.device(device).index or 0)
+    vp = lambda a: None if a is None else C.c_void_p(a.ctypes.data)  # noqa: E731
+    _lib.check(_lib.load().m3s_match_iterative_proj_host(
+        vp(x11), vp(x21), vp(d11), vp(d21), vp(init), vp(idx_a), vp(valid_a), b, h, w, d,
+        int(max_iter), float(lambda_init), float(convergence_thresh), int(radius), int(dilation_max),
+        float(dist_thresh), int(chunk_pairs), int(dev_index)), "match_iterative_proj_host")
+    idx_r = idx_a.reshape(b, h * w)
+    valid_r = valid_a.reshape(b, h * w).view(np.bool_)[:, :, None]
+    if as_torch:
+        return torch.from_numpy(idx_r), torch.from_numpy(valid_r)
+    return idx_r, valid_r
 
 
 # ---------------------------------------------------------------------------------------------

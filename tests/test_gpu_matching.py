@@ -243,6 +243,38 @@ def test_match_pipeline_vs_oracle(K, oracle, synth, desc):
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
 
 
+def test_match_host_pipeline(K, oracle, synth):
+    """m3s_match_iterative_proj_host: chunked upload / compute / download on rotating streams gives
+    the same result as the oracle for ragged chunking, with an initial correspondence, without
+    refinement, with pinned torch inputs and caller-provided pinned outputs"""
+    import torch
+    ps = synth.make_pairs([11, 12, 13, 14, 15, 16, 17], 48, 64, 24, "dyadic")
+    a = (ps["X11"], ps["X21"], ps["D11"], ps["D21"])
+    idx_o, valid_o = oracle.match_iterative_proj(*a)
+    for chunk in (1, 2, 3, 7, 64):
+        idx, valid = K.match_iterative_proj_host(*a, chunk_pairs=chunk)
+        assert isinstance(idx, np.ndarray) and idx.dtype == np.int32 and valid.dtype == np.bool_
+        assert valid.shape == (7, 48 * 64, 1)
+        assert np.array_equal(idx, idx_o) and np.array_equal(valid, valid_o), chunk
+    # numpy inputs to the generic entry point take the same route
+    idx, valid = K.match_iterative_proj_device(*a)
+    assert np.array_equal(idx, idx_o) and np.array_equal(valid, valid_o)
+    # initial correspondence, no refinement
+    r = oracle.match_iterative_proj(*a, idx_o.copy(), radius=0)
+    g = K.match_iterative_proj_host(*a, idx_o.copy(), radius=0, chunk_pairs=2)
+    assert np.array_equal(g[0], r[0]) and np.array_equal(g[1], r[1])
+    # pinned torch tensors in, caller-provided pinned outputs
+    pin = [torch.from_numpy(x).pin_memory() for x in a]
+    out_idx = torch.empty((7, 48 * 64), dtype=torch.int32).pin_memory()
+    out_valid = torch.empty((7, 48 * 64), dtype=torch.uint8).pin_memory()
+    ti, tv = K.match_iterative_proj_host(*pin, chunk_pairs=2, out=(out_idx, out_valid))
+    assert isinstance(ti, torch.Tensor) and ti.data_ptr() == out_idx.data_ptr()
+    assert np.array_equal(ti.numpy(), idx_o) and np.array_equal(tv.numpy(), valid_o)
+    # empty batch
+    e = K.match_iterative_proj_host(*(x[:0] for x in a))
+    assert e[0].shape == (0, 48 * 64)
+
+
 def test_l2_match_entry_point(K, oracle, synth):
     from mast3r_slam_b200 import matching
     from mast3r_slam_b200.config import set_config
