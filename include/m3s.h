@@ -192,10 +192,14 @@ int m3s_gn_plan_ld(const m3s_gn_plan* plan);            /* row stride of H: dim 
 #define M3S_GN_EDGE_STRIDE 36
 double* m3s_gn_plan_edge_blocks(m3s_gn_plan* plan, int64_t* count_out);
 double* m3s_gn_plan_H(m3s_gn_plan* plan);   /* [dim rows, ld] f64 (device): H + 1e-6 I after
-                                               m3s_gn_assemble; overwritten by its Cholesky
-                                               factor (lower) in m3s_gn_solve_update */
+                                               m3s_gn_assemble; used as the factorisation's work
+                                               matrix (destroyed) by m3s_gn_solve_update */
 double* m3s_gn_plan_g(m3s_gn_plan* plan);   /* [dim] */
 double* m3s_gn_plan_dx(m3s_gn_plan* plan);  /* [dim] last solved step */
+/* Development aid: with M3S_GN_TIMELINE=1 in the environment when the plan is created, the solve
+ * kernels stamp %globaltimer (ns) at entry / exit: [4 kinds (diag, panel, syrk, backsolve)]
+ * [dim/32 blocks][2] int64 on the device; NULL / 0 when disabled. */
+long long* m3s_gn_plan_timeline(m3s_gn_plan* plan, int64_t* count_out);
 double* m3s_gn_plan_poses(m3s_gn_plan* plan); /* [num_kf, 8] f64: the solver's pose state
                                                  (gauss_newton.py:92, Twc.astype(float64)) */
 

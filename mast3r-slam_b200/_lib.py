@@ -60,6 +60,7 @@ SIGNATURES = {
     "m3s_gn_plan_g": (_vp, [_vp]),
     "m3s_gn_plan_dx": (_vp, [_vp]),
     "m3s_gn_plan_poses": (_vp, [_vp]),
+    "m3s_gn_plan_timeline": (_vp, [_vp, C.POINTER(C.c_int64)]),
     "m3s_gn_set_poses": (_i, [_vp, _vp, _vp]),
     "m3s_gn_get_poses": (_i, [_vp, _vp, _vp]),
     "m3s_gn_accumulate": (_i, [_vp, C.POINTER(GNParams), _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),

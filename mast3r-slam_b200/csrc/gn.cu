@@ -698,40 +698,80 @@ __global__ void gn_pad_diag_kernel(const Status* __restrict__ status, double* __
 }
 
 // ------------------------------------------------------------------------------------------------
-// Blocked right-looking Cholesky of the augmented matrix (lower triangle, in place), panel = 32.
-//   step k: (a) every CTA factorises the 32x32 diagonal block redundantly in shared memory (no
-//               extra launch / grid sync), CTA 0 stores it to Ldiag[k]; each thread then solves
-//               one row of the panel below:  L21 = A21 L11^-T  (right-looking inside the row,
-//               row in registers);
-//           (b) trailing update A22 -= L21 L21^T on 64x64 tiles of the lower triangle (+ rhs row).
+// Blocked right-looking Cholesky of the augmented matrix, NB = 32: ONE kernel per block step, a
+// single dependent chain of 44 launches for the 200-keyframe graph (dim 1393).
+//
+// chol_step_kernel(k) holds three kinds of CTAs:
+//   * update tiles (64x64 of the trailing lower triangle, incl. the rhs row): each tile solves the
+//     64 + 64 panel rows it needs against L_k itself (one row per thread in registers, L_k from
+//     Ldiag[k]) and applies the rank-32 update  A22 -= L21 L21^T  (4x4 register tiles).  The panel
+//     solve is recomputed per tile (~1 us) instead of being a kernel of its own: every dependent
+//     launch costs 2.5 us, a join of two graph branches 7 us (measured with the timeline below).
+//     Tiles of tile-column 0 store their solved rows to a SEPARATE matrix Lm (the factor the
+//     back-substitution reads), so no tile overwrites panel rows another tile still has to read.
+//   * the diag CTA brings the NEXT diagonal block up to date on its own -- B = A[k+1,k] L_k^-T,
+//     D = A[k+1,k+1] - B B^T -- and factorises it with one warp (chol32_warp), so the 32 dependent
+//     column steps of block k+1 overlap the trailing update of step k instead of preceding step
+//     k+1.  Update tiles leave block (k+1,k+1) alone.
+//   * one CTA inverts L_k for the back-substitution, off the chain.
+// chol_diag0_kernel factorises block 0 before the first step.
 // ------------------------------------------------------------------------------------------------
-constexpr int kTrsmRows = 128;
+constexpr int kStepThreads = 256;
 
-// 32x32 Cholesky in shared memory by the whole CTA (128 threads), ONE barrier per column:
-// every thread derives 1/d_jj itself (rsqrt, no broadcast step); the trailing update uses the
-// unscaled column,  D[r][c] -= D[r][j] D[c][j] / d_jj,  and the scaled column goes to a separate
-// array L (no write-after-read hazard inside a column step).  dinv[j] = 1 / L[j][j].
-__device__ __forceinline__ void chol32_smem(double (*D)[kNB + 1], double (*L)[kNB + 1], double* dinv,
-                                            int* bad) {
-    const int tid = threadIdx.x;
-    const int tc = tid & 31, tr = tid >> 5;
-    for (int j = 0; j < kNB; ++j) {
-        double djj = D[j][j];
-        if (!((djj > 0.0) && (djj < 1e300))) { if (tid == 0) *bad = 1; djj = 1.0; }
-        const double rs = rsqrt(djj);       // 1 / l_jj
-        const double inv_d = rs * rs;       // 1 / d_jj
-        if (tr == 0) {
-            // warp 0: column j of L (rows >= j), zeros above the diagonal
-            L[tc][j] = (tc > j) ? D[tc][j] * rs : ((tc == j) ? djj * rs : 0.0);
-            if (tc == j) dinv[j] = rs;
-        }
-        if (tc > j) {
-            const double cj = D[tc][j] * inv_d;
-            for (int r = j + 1 + tr; r < kNB; r += kTrsmRows / 32)
-                if (tc <= r) D[r][tc] -= D[r][j] * cj;
-        }
-        __syncthreads();
+// Optional timeline (M3S_GN_TIMELINE=1 at plan creation): %globaltimer stamps at entry / exit into
+// tl[(kind * nblk + kb) * 2 + {0,1}]: kind 0 = diag CTA of block kb, 1 = update tile (0,0) of step
+// kb until its panel rows are solved, 2 = the same tile until its update is stored, 3 = back-
+// substitution CTA of block kb.  nullptr = disabled.
+__device__ __forceinline__ void tl_stamp(long long* tl, int slot) {
+    if (tl != nullptr) {
+        long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        tl[slot] = t;
     }
+}
+
+// 1 / sqrt(d) for 1e-290 < d < 1e300: hardware seed (2^-22) + two Newton steps, no special cases
+__device__ __forceinline__ double rsqrt_fast(double d) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+    const double h = 0.5 * d;
+    double e = fma(-h * y, y, 0.5);
+    y = fma(y, e, y);
+    e = fma(-h * y, y, 0.5);
+    return fma(y, e, y);
+}
+
+// 32x32 Cholesky by ONE warp, row `lane` of the block in registers; no shared memory and no
+// barrier on the 32-step dependent chain, so the whole factorisation is straight-line code the
+// scheduler can interleave.  Column j: the diagonal d_j and the entry a[j+1][j] are broadcast by
+// two independent shuffles, every lane derives rs = 1/sqrt(d_j) itself, scales its own entry
+// (l = a[j] rs) and updates the NEXT column first (a[j+1] -= l * a[j+1][j] rs: the only update the
+// next step waits for); the remaining columns follow with l broadcast from lane c by shuffle.
+// Entries above the diagonal pick up finite garbage that nothing reads.
+// (A block-wide version with one __syncthreads per column took 12 us per block, a warp version
+//  going through shared memory 8 us; measured with scripts/gn_solve_timeline.py.)
+__device__ __forceinline__ bool chol32_warp(double (*W)[kNB + 1], double (*L)[kNB + 1], double* dinv,
+                                            int lane) {
+    double a[kNB];
+#pragma unroll
+    for (int c = 0; c < kNB; ++c) a[c] = (c <= lane) ? W[lane][c] : 0.0;
+    bool bad = false;
+#pragma unroll
+    for (int j = 0; j < kNB; ++j) {
+        double d = __shfl_sync(0xffffffffu, a[j], j);
+        const double nxt = __shfl_sync(0xffffffffu, a[j], (j + 1) & 31);  // a[j+1][j]
+        if (!((d > 1e-290) && (d < 1e300))) { bad = true; d = 1.0; }      // warp-uniform
+        const double rs = rsqrt_fast(d);
+        const double l = (lane == j) ? d * rs : a[j] * rs;
+        a[j] = l;
+        if (lane == j) dinv[j] = rs;
+        if (j + 1 < kNB) a[j + 1] -= l * (nxt * rs);
+#pragma unroll
+        for (int c = j + 2; c < kNB; ++c) a[c] -= l * __shfl_sync(0xffffffffu, l, c);
+    }
+#pragma unroll
+    for (int c = 0; c < kNB; ++c) L[lane][c] = (c <= lane) ? a[c] : 0.0;
+    return !bad;
 }
 
 // Column `lane` of the inverse of the lower-triangular 32x32 block L (shared memory), by forward
@@ -750,89 +790,196 @@ __device__ __forceinline__ void tri_inverse32(double (*L)[kNB + 1], const double
     for (int r = 0; r < kNB; ++r) out[r * kNB + lane] = x[r];
 }
 
-// grid = row tiles of the panel below the diagonal block (incl. the rhs row) + 1 extra CTA that
-// inverts the diagonal factor (used by the back-substitution).
-__global__ void __launch_bounds__(kTrsmRows)
-chol_panel_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* __restrict__ Ldiag,
-                  double* __restrict__ Linv, int np, int k0) {
-    if (status->stopped | status->failed | status->chol_fail) return;
-    __shared__ double W[kNB][kNB + 1];  // working copy of the diagonal block
-    __shared__ double D[kNB][kNB + 1];  // its Cholesky factor (lower)
-    __shared__ double dinv[kNB];
-    __shared__ int bad;
-    const int tid = threadIdx.x;
-    for (int i = tid; i < kNB * kNB; i += blockDim.x) {
+struct DiagSmem {
+    double W[kNB][kNB + 1];   // block being factorised
+    double L[kNB][kNB + 1];   // previous factor, then this block's factor
+    double Bm[kNB][kNB + 1];  // B = L[kb, kb-1]
+    double dinv[kNB];
+    int bad;
+};
+
+// Factorise diagonal block kb (whole CTA, any blockDim >= 32):
+//   Ldiag[kb] <- chol(A[kb,kb] - B B^T),  B = A[kb,kb-1] L_{kb-1}^-T   (kb > 0),
+// with A[kb,kb-1] read from Hm (final after step kb-2; step kb-1 does not touch it because solved
+// panel rows go to Lm, not back into Hm).
+__device__ __forceinline__ void chol_diag_block(DiagSmem& sm, Status* __restrict__ status,
+                                                const double* __restrict__ Hm, double* __restrict__ Lm,
+                                                double* __restrict__ Ldiag, double* __restrict__ Linv,
+                                                int np, int kb, long long* __restrict__ tl) {
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int k0 = kb * kNB;
+    const int nblk = np / kNB;
+    if (tid == 0) tl_stamp(tl, (0 * nblk + kb) * 2);
+    for (int i = tid; i < kNB * kNB; i += nt) {
         const int r = i / kNB, c = i % kNB;
-        W[r][c] = (c <= r) ? Hm[(size_t)(k0 + r) * np + k0 + c] : 0.0;
+        sm.W[r][c] = (c <= r) ? Hm[(size_t)(k0 + r) * np + k0 + c] : 0.0;
     }
-    if (tid == 0) bad = 0;
+    if (tid == 0) sm.bad = 0;
+    if (kb > 0) {
+        const double* Lp = Ldiag + (size_t)(kb - 1) * kNB * kNB;
+        for (int i = tid; i < kNB * kNB; i += nt) {
+            sm.L[i / kNB][i % kNB] = Lp[i];
+            sm.Bm[i / kNB][i % kNB] = Hm[(size_t)(k0 + i / kNB) * np + (k0 - kNB) + (i % kNB)];
+        }
+        __syncthreads();
+        if (tid < kNB) sm.dinv[tid] = 1.0 / sm.L[tid][tid];
+        __syncthreads();
+        if (tid < kNB) {
+            // row tid of B: right-looking substitution against L_{kb-1}, row in registers
+            double x[kNB];
+#pragma unroll
+            for (int c = 0; c < kNB; ++c) x[c] = sm.Bm[tid][c];
+#pragma unroll
+            for (int j = 0; j < kNB; ++j) {
+                const double xj = x[j] * sm.dinv[j];
+                x[j] = xj;
+#pragma unroll
+                for (int c = j + 1; c < kNB; ++c) x[c] -= xj * sm.L[c][j];
+            }
+#pragma unroll
+            for (int c = 0; c < kNB; ++c) sm.Bm[tid][c] = x[c];
+        }
+        __syncthreads();
+        // W -= B B^T (lower part)
+        for (int i = tid; i < kNB * kNB; i += nt) {
+            const int r = i / kNB, c = i % kNB;
+            if (c <= r) {
+                double s = 0.0;
+#pragma unroll 8
+                for (int j = 0; j < kNB; ++j) s += sm.Bm[r][j] * sm.Bm[c][j];
+                sm.W[r][c] -= s;
+            }
+        }
+    }
     __syncthreads();
-    chol32_smem(W, D, dinv, &bad);
-    if (bad) {
-        if (blockIdx.x == 0 && tid == 0) status->chol_fail = 1;
+    if (tid < 32) {
+        if (!chol32_warp(sm.W, sm.L, sm.dinv, tid) && tid == 0) sm.bad = 1;
+    }
+    __syncthreads();
+    if (sm.bad) {
+        if (tid == 0) status->chol_fail = 1;
         return;
     }
-    if (blockIdx.x == gridDim.x - 1) {
-        // extra CTA: publish L11; its inverse (for the back-substitution) is computed off the
-        // critical path by an extra CTA of the following syrk kernel, or here for the last panel.
-        double* Ld = Ldiag + (size_t)(k0 / kNB) * kNB * kNB;
-        for (int i = tid; i < kNB * kNB; i += blockDim.x) Ld[i] = D[i / kNB][i % kNB];
-        if (k0 + kNB >= np && tid < 32) tri_inverse32(D, dinv, Linv + (size_t)(k0 / kNB) * kNB * kNB, tid);
-        return;
+    double* Ld = Ldiag + (size_t)kb * kNB * kNB;
+    for (int i = tid; i < kNB * kNB; i += nt) {
+        const int r = i / kNB, c = i % kNB;
+        Ld[i] = sm.L[r][c];
+        if (c <= r) Lm[(size_t)(k0 + r) * np + k0 + c] = sm.L[r][c];
     }
-    // rows below the diagonal block, including the rhs row np
-    const int row = k0 + kNB + blockIdx.x * kTrsmRows + tid;
-    if (row > np) return;
-    double* a = Hm + (size_t)row * np + k0;
-    double x[kNB];
-#pragma unroll
-    for (int c = 0; c < kNB; ++c) x[c] = a[c];
-#pragma unroll
-    for (int j = 0; j < kNB; ++j) {
-        const double xj = x[j] * dinv[j];
-        x[j] = xj;
-#pragma unroll
-        for (int c = j + 1; c < kNB; ++c) x[c] -= xj * D[c][j];
-    }
-#pragma unroll
-    for (int c = 0; c < kNB; ++c) a[c] = x[c];
+    // the last block has no following step whose spare CTA could invert it
+    if (kb == nblk - 1 && tid < 32) tri_inverse32(sm.L, sm.dinv, Linv + (size_t)kb * kNB * kNB, tid);
+    __syncthreads();
+    if (tid == 0) tl_stamp(tl, (0 * nblk + kb) * 2 + 1);
+}
+
+__global__ void __launch_bounds__(kStepThreads)
+chol_diag0_kernel(Status* __restrict__ status, const double* __restrict__ Hm, double* __restrict__ Lm,
+                  double* __restrict__ Ldiag, double* __restrict__ Linv, int np,
+                  long long* __restrict__ tl) {
+    if (status->stopped | status->failed | status->chol_fail) return;
+    __shared__ DiagSmem sm;
+    chol_diag_block(sm, status, Hm, Lm, Ldiag, Linv, np, 0, tl);
 }
 
 constexpr int kSyrkTile = 64;
 
-__global__ void __launch_bounds__(256)
-chol_syrk_kernel(const Status* __restrict__ status, double* __restrict__ Hm,
-                 const double* __restrict__ Ldiag, double* __restrict__ Linv, int np, int k0) {
+struct TileSmem {
+    double D[kNB][kNB + 1];        // L_k
+    double dinv[kNB];
+    double A[kSyrkTile][kNB + 1];  // panel rows of the tile's row range
+    double B[kSyrkTile][kNB + 1];  // panel rows of the tile's column range
+};
+
+union StepSmem {
+    TileSmem t;
+    DiagSmem d;
+};
+
+// grid = (max(#tile columns, 1), #tile rows + 2); blockIdx.y == #tile rows: CTA x == 0 inverts L_kb,
+// blockIdx.y == #tile rows + 1: CTA x == 0 is the diag CTA of block kb + 1.
+__global__ void __launch_bounds__(kStepThreads)
+chol_step_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* __restrict__ Lm,
+                 double* __restrict__ Ldiag, double* __restrict__ Linv, int np, int kb,
+                 long long* __restrict__ tl) {
     if (status->stopped | status->failed | status->chol_fail) return;
+    __shared__ StepSmem sm;
+    const int tid = threadIdx.x;
+    const int nblk = np / kNB;
+    const int k0 = kb * kNB;
+    const int ntr = (int)gridDim.y - 2;
     const int tr = blockIdx.y, tc = blockIdx.x;
-    if (tr == (int)gridDim.y - 1) {
-        // extra CTA row: block (0) inverts the diagonal factor of this step, concurrently with the
-        // trailing update (off the factorisation's critical path)
-        if (tc != 0) return;
-        __shared__ double Ls[kNB][kNB + 1];
-        __shared__ double di[kNB];
-        const double* Ld = Ldiag + (size_t)(k0 / kNB) * kNB * kNB;
-        for (int i = threadIdx.x; i < kNB * kNB; i += blockDim.x) Ls[i / kNB][i % kNB] = Ld[i];
+    if (tr == ntr + 1) {
+        if (tc == 0 && kb + 1 < nblk) chol_diag_block(sm.d, status, Hm, Lm, Ldiag, Linv, np, kb + 1, tl);
+        return;
+    }
+    if (tr == ntr) {
+        // invert L_kb for the back-substitution (the last block is inverted by its own diag CTA)
+        if (tc != 0 || kb == nblk - 1) return;
+        const double* Ld = Ldiag + (size_t)kb * kNB * kNB;
+        for (int i = tid; i < kNB * kNB; i += kStepThreads) sm.t.D[i / kNB][i % kNB] = Ld[i];
         __syncthreads();
-        if (threadIdx.x < kNB) di[threadIdx.x] = 1.0 / Ls[threadIdx.x][threadIdx.x];
+        if (tid < kNB) sm.t.dinv[tid] = 1.0 / sm.t.D[tid][tid];
         __syncthreads();
-        if (threadIdx.x < 32) tri_inverse32(Ls, di, Linv + (size_t)(k0 / kNB) * kNB * kNB, threadIdx.x);
+        if (tid < 32) tri_inverse32(sm.t.D, sm.t.dinv, Linv + (size_t)kb * kNB * kNB, tid);
         return;
     }
     if (tc > tr) return;
+    const bool first = (tr == 0) && (tc == 0);
+    const bool stamp = (tl != nullptr) && first && (tid == 0);
+    if (stamp) tl_stamp(tl, (1 * nblk + kb) * 2);
     const int base = k0 + kNB;
     const int r0 = base + tr * kSyrkTile, c0 = base + tc * kSyrkTile;
-    __shared__ double A[kSyrkTile][kNB + 1];
-    __shared__ double B[kSyrkTile][kNB + 1];
-    const int tid = threadIdx.x;
-    for (int i = tid; i < kSyrkTile * kNB; i += 256) {
+    const int ty = tid / 16, tx = tid % 16;  // 16 x 16 threads, 4 x 4 outputs each (strided by 16)
+    // the tile's current values first: their latency hides behind the panel solve
+    double cval[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int gr = r0 + ty + 16 * i;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int gc = c0 + tx + 16 * j;
+            cval[i][j] = (gr <= np && gc < np && gc <= gr) ? Hm[(size_t)gr * np + gc] : 0.0;
+        }
+    }
+    {
+        const double* Ld = Ldiag + (size_t)kb * kNB * kNB;
+        for (int i = tid; i < kNB * kNB; i += kStepThreads) sm.t.D[i / kNB][i % kNB] = Ld[i];
+    }
+    for (int i = tid; i < kSyrkTile * kNB; i += kStepThreads) {
         const int r = i / kNB, c = i % kNB;
         const int gr = r0 + r, gc = c0 + r;
-        A[r][c] = (gr <= np) ? Hm[(size_t)gr * np + k0 + c] : 0.0;
-        B[r][c] = (gc < np) ? Hm[(size_t)gc * np + k0 + c] : 0.0;
+        sm.t.A[r][c] = (gr <= np) ? Hm[(size_t)gr * np + k0 + c] : 0.0;
+        if (tc != tr) sm.t.B[r][c] = (gc < np) ? Hm[(size_t)gc * np + k0 + c] : 0.0;
     }
     __syncthreads();
-    const int ty = tid / 16, tx = tid % 16;  // 16 x 16 threads, 4 x 4 outputs each (strided by 16)
+    if (tid < kNB) sm.t.dinv[tid] = 1.0 / sm.t.D[tid][tid];
+    __syncthreads();
+    // panel solve: threads 0..63 take the rows of A, threads 64..127 the rows of B
+    if (tid < kSyrkTile || (tid < 2 * kSyrkTile && tc != tr)) {
+        double (*P)[kNB + 1] = (tid < kSyrkTile) ? sm.t.A : sm.t.B;
+        const int r = tid & (kSyrkTile - 1);
+        double x[kNB];
+#pragma unroll
+        for (int c = 0; c < kNB; ++c) x[c] = P[r][c];
+#pragma unroll
+        for (int j = 0; j < kNB; ++j) {
+            const double xj = x[j] * sm.t.dinv[j];
+            x[j] = xj;
+#pragma unroll
+            for (int c = j + 1; c < kNB; ++c) x[c] -= xj * sm.t.D[c][j];
+        }
+#pragma unroll
+        for (int c = 0; c < kNB; ++c) P[r][c] = x[c];
+    }
+    __syncthreads();
+    if (stamp) { tl_stamp(tl, (1 * nblk + kb) * 2 + 1); tl_stamp(tl, (2 * nblk + kb) * 2); }
+    double (*Bp)[kNB + 1] = (tc == tr) ? sm.t.A : sm.t.B;
+    if (tc == 0) {  // this tile column publishes the solved rows (the factor's block column kb)
+        for (int i = tid; i < kSyrkTile * kNB; i += kStepThreads) {
+            const int r = i / kNB, c = i % kNB;
+            if (r0 + r <= np) Lm[(size_t)(r0 + r) * np + k0 + c] = sm.t.A[r][c];
+        }
+    }
     double acc[4][4];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
@@ -842,7 +989,7 @@ chol_syrk_kernel(const Status* __restrict__ status, double* __restrict__ Hm,
     for (int k = 0; k < kNB; ++k) {
         double a[4], b[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { a[i] = A[ty + 16 * i][k]; b[i] = B[tx + 16 * i][k]; }
+        for (int i = 0; i < 4; ++i) { a[i] = sm.t.A[ty + 16 * i][k]; b[i] = Bp[tx + 16 * i][k]; }
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -855,15 +1002,19 @@ chol_syrk_kernel(const Status* __restrict__ status, double* __restrict__ Hm,
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int gc = c0 + tx + 16 * j;
-            if (gc < np && gc <= gr) Hm[(size_t)gr * np + gc] -= acc[i][j];
+            if (!(gc < np && gc <= gr)) continue;
+            // block (kb+1, kb+1) belongs to the diag CTA of this launch
+            if (first && gr < base + kNB) continue;
+            Hm[(size_t)gr * np + gc] = cval[i][j] - acc[i][j];
         }
     }
+    if (stamp) tl_stamp(tl, (2 * nblk + kb) * 2 + 1);
 }
 
 // ------------------------------------------------------------------------------------------------
 // Back-substitution L^T dx = y (y = rhs row of the factorised augmented matrix), ||dx|| test
 // (gauss_newton.py:263-265: stop BEFORE applying) and Sim3 retraction (sim3_ops.py:129-251) in one
-// single-CTA kernel.
+// kernel.
 // ------------------------------------------------------------------------------------------------
 __device__ void sim3_retract_dev(const double* xi, double* T) {
     const double EPS = 1e-6;
@@ -904,67 +1055,126 @@ __device__ void sim3_retract_dev(const double* xi, double* T) {
     T[7] = s * T[7];
 }
 
-constexpr int kSolveThreads = 1024;
+// Dataflow back-substitution.  One CTA per 32-column block; the CTA with blockIdx i owns block
+// b = nblk-1-i, so every CTA waits only on CTAs with a smaller blockIdx (dispatched before it: no
+// deadlock even if the grid were not fully resident).  CTA b accumulates
+//     s_b = sum_{r > b} L[r, b]^T x_r
+// block by block as the x_r are published (r descending): the 32x32 tile of L for the next r is
+// already in registers when its flag arrives, so a step of the critical path is flag -> 256-B read of
+// x_r -> 4 FMAs per thread -> (for r = b+1) shared-memory reduction -> x_b = Linv_b^T (y_b - s_b)
+// -> publish.  Flags carry the launch epoch (no reset pass).  The CTA of block 0 finishes last by
+// construction; it then does the ||dx|| test BEFORE applying (gauss_newton.py:263-265) and the Sim3
+// retraction (sim3_ops.py:129-251).
+constexpr int kBackThreads = 256;
+constexpr int kSpinLimit = 1 << 24;
 
-__global__ void __launch_bounds__(kSolveThreads)
+__device__ __forceinline__ int ld_acquire(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(int* p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(kBackThreads)
 gn_backsolve_update_kernel(Status* __restrict__ status, const double* __restrict__ Hm,
                            const double* __restrict__ Linv, int np, int dim, int num_free,
                            const int* __restrict__ free_kf, double delta_thresh,
-                           double* __restrict__ dx_out, double* __restrict__ poses) {
+                           double* __restrict__ xsol, int* __restrict__ flags, int epoch,
+                           double* __restrict__ dx_out, double* __restrict__ poses,
+                           long long* __restrict__ tl) {
     if (status->stopped | status->failed) return;
-    extern __shared__ double ysh[];  // [np]
-    __shared__ double red[kSolveThreads / 32];
-    __shared__ double Lsh[kNB * kNB];
-    __shared__ double xsh[kNB];
-    __shared__ int decision;  // 0 apply, 1 stop, 2 fail
+    const int nblk = np / kNB;
+    const int b = nblk - 1 - (int)blockIdx.x;
     const int tid = threadIdx.x;
+    if (tid == 0) tl_stamp(tl, (3 * nblk + b) * 2);
     if (status->chol_fail) {
-        if (tid == 0) { status->failed = 1; status->attempted += 1; status->chol_fail = 0; }
+        // every CTA sees the same flag (nobody clears it here); the last one records the failure
+        if (b == 0 && tid == 0) { status->failed = 1; status->attempted += 1; }
         return;
     }
-    for (int i = tid; i < np; i += blockDim.x) ysh[i] = Hm[(size_t)np * np + i];
-    __syncthreads();
-    const int nblk = np / kNB;
-    for (int b = nblk - 1; b >= 0; --b) {
-        // x_b = L_bb^-T y_b = sum_r Linv[r][i] y_r: Linv block staged by all 1024 threads, then
-        // one 32-term dot product per lane of warp 0
-        Lsh[tid] = Linv[(size_t)b * kNB * kNB + tid];
-        __syncthreads();
-        if (tid < 32) {
-            double acc = 0.0;
+    __shared__ double Li[kNB][kNB + 1];               // Linv_b
+    __shared__ double xr[kNB];                         // x_r of the block being applied
+    __shared__ double part[kBackThreads / 32][kNB];    // per-row-group partial sums
+    __shared__ double rhs[kNB];
+    __shared__ int ok_s;
+    const int c = tid & 31, g = tid >> 5;              // column c of the block, row group g (4 rows)
+    for (int i = tid; i < kNB * kNB; i += kBackThreads) Li[i / kNB][i % kNB] = Linv[(size_t)b * kNB * kNB + i];
+    double acc = 0.0;
+    // tile of L for block row r, column block b: thread (c, g) holds rows 4g .. 4g+3 of column c
+    double t[4];
+    int r = nblk - 1;
+    if (r > b) {
 #pragma unroll
-            for (int r = 0; r < kNB; ++r) acc += Lsh[r * kNB + tid] * ysh[b * kNB + r];
-            xsh[tid] = acc;
-        }
-        __syncthreads();
-        if (tid < 32) ysh[b * kNB + tid] = xsh[tid];
-        // y_c -= sum_{r in block b} L[r][c] x_r  for all columns c left of the block
-        const int ncol = b * kNB;
-        for (int c = tid; c < ncol; c += blockDim.x) {
-            double sacc = ysh[c];
-            const double* Lr = Hm + (size_t)(b * kNB) * np + c;
-#pragma unroll 8
-            for (int r = 0; r < kNB; ++r) sacc -= Lr[(size_t)r * np] * xsh[r];
-            ysh[c] = sacc;
-        }
-        __syncthreads();
+        for (int i = 0; i < 4; ++i) t[i] = Hm[(size_t)(r * kNB + 4 * g + i) * np + b * kNB + c];
     }
-    // ||dx||_2 and finiteness
-    double part = 0.0;
+    for (; r > b; --r) {
+        if (tid == 0) {
+            int spins = 0, okv = 1;
+            while (ld_acquire(flags + r) != epoch) {
+                if (++spins > kSpinLimit) { okv = 0; break; }
+                __nanosleep(20);
+            }
+            ok_s = okv;
+        }
+        __syncthreads();
+        if (!ok_s) {  // cannot happen with in-order dispatch; never hang the device
+            if (tid == 0) status->failed = 1;
+            return;
+        }
+        if (tid < kNB) xr[tid] = __ldcg(xsol + r * kNB + tid);
+        __syncthreads();
+        double cur[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) cur[i] = t[i];
+        if (r - 1 > b) {  // prefetch the next tile before using this one
+#pragma unroll
+            for (int i = 0; i < 4; ++i) t[i] = Hm[(size_t)((r - 1) * kNB + 4 * g + i) * np + b * kNB + c];
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc += cur[i] * xr[4 * g + i];
+        __syncthreads();  // xr is rewritten in the next round
+    }
+    part[g][c] = acc;
+    __syncthreads();
+    if (tid < kNB) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < kBackThreads / 32; ++w) s += part[w][tid];
+        rhs[tid] = Hm[(size_t)np * np + b * kNB + tid] - s;  // y_b - s_b
+    }
+    __syncthreads();
+    if (tid < kNB) {
+        // x_b[i] = sum_r Linv[r][i] rhs[r]   (Linv lower triangular: r >= i)
+        double s = 0.0;
+#pragma unroll
+        for (int rr = 0; rr < kNB; ++rr) s += Li[rr][tid] * rhs[rr];
+        __stcg(xsol + b * kNB + tid, s);
+        __threadfence();
+    }
+    __syncthreads();
+    if (tid == 0) { st_release(flags + b, epoch); tl_stamp(tl, (3 * nblk + b) * 2 + 1); }
+    if (b != 0) return;
+
+    // ---- block 0: all of x is published (x_0 depended on every other block) ----------------------
+    __shared__ double red[kBackThreads / 32];
+    __shared__ int decision;  // 0 apply, 1 stop, 2 fail
+    double psum = 0.0;
     int nonfinite = 0;
-    for (int i = tid; i < dim; i += blockDim.x) {
-        const double v = ysh[i];
+    for (int i = tid; i < dim; i += kBackThreads) {
+        const double v = __ldcg(xsol + i);
         dx_out[i] = v;
-        part += v * v;
+        psum += v * v;
         if (!(fabs(v) <= 1.7e308)) nonfinite = 1;
     }
-    part = warp_sum(part);
+    psum = warp_sum(psum);
     nonfinite = __any_sync(0xffffffffu, nonfinite);
-    if ((tid & 31) == 0) red[tid >> 5] = nonfinite ? __longlong_as_double(0x7ff8000000000000LL) : part;
+    if ((tid & 31) == 0) red[tid >> 5] = nonfinite ? __longlong_as_double(0x7ff8000000000000LL) : psum;
     __syncthreads();
     if (tid == 0) {
         double s = 0.0;
-        for (int w = 0; w < kSolveThreads / 32; ++w) s += red[w];
+        for (int w = 0; w < kBackThreads / 32; ++w) s += red[w];
         const double nrm = sqrt(s);
         status->last_norm = nrm;
         status->attempted += 1;
@@ -979,7 +1189,12 @@ gn_backsolve_update_kernel(Status* __restrict__ status, const double* __restrict
     }
     __syncthreads();
     if (decision != 0) return;
-    for (int f = tid; f < num_free; f += blockDim.x) sim3_retract_dev(ysh + 7 * f, poses + 8 * free_kf[f]);
+    for (int f = tid; f < num_free; f += kBackThreads) {
+        double xi[7];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) xi[k] = __ldcg(xsol + 7 * f + k);
+        sim3_retract_dev(xi, poses + 8 * free_kf[f]);
+    }
 }
 
 __global__ void gn_poses_f32_to_f64(const float* __restrict__ in, double* __restrict__ out, int n,
@@ -1024,6 +1239,11 @@ struct m3s_gn_plan {
     double* Hm = nullptr;           // [np + 1, np]
     double* Ldiag = nullptr;        // [np / 32, 32, 32] diagonal factor blocks
     double* Linv = nullptr;         // [np / 32, 32, 32] their inverses
+    double* Lm = nullptr;           // [np + 1, np] the Cholesky factor (block columns below the
+                                    // diagonal + diagonal blocks) and, in row np, y = L^-1 (-g)
+    double* xsol = nullptr;         // [np] back-substitution result blocks
+    int* flags = nullptr;           // [np / 32] publication flags of the back-substitution
+    long long* timeline = nullptr;  // [4, np / 32, 2] globaltimer stamps (M3S_GN_TIMELINE=1), else null
     double* g = nullptr;            // [dim]
     double* dx = nullptr;           // [dim]
     Status* status = nullptr;
@@ -1037,6 +1257,7 @@ static void plan_free(m3s_gn_plan* p) {
     if (!p) return;
     if (p->graph_exec) cudaGraphExecDestroy(p->graph_exec);
     if (p->graph) cudaGraphDestroy(p->graph);
+    cudaFree(p->Lm); cudaFree(p->xsol); cudaFree(p->flags); cudaFree(p->timeline);
     cudaFree(p->poses); cudaFree(p->meta); cudaFree(p->partials); cudaFree(p->edge_blocks);
     cudaFree(p->blocks); cudaFree(p->list_edge); cudaFree(p->list_sign); cudaFree(p->free_kf);
     cudaFree(p->Hm); cudaFree(p->Ldiag); cudaFree(p->Linv); cudaFree(p->g); cudaFree(p->dx); cudaFree(p->status);
@@ -1163,6 +1384,16 @@ M3S_API m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii, const int32_t* jj, in
     ok = ok && cudaMalloc((void**)&p->Hm, sizeof(double) * hm) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&p->Ldiag, sizeof(double) * kNB * std::max(p->np, kNB)) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&p->Linv, sizeof(double) * kNB * std::max(p->np, kNB)) == cudaSuccess;
+    const int nblk = std::max(p->np / kNB, 1);
+    ok = ok && cudaMalloc((void**)&p->Lm, sizeof(double) * (size_t)(p->np + 1) * std::max(p->np, 1)) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&p->xsol, sizeof(double) * std::max(p->np, kNB)) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&p->flags, sizeof(int) * nblk) == cudaSuccess;
+    if (const char* tlv = getenv("M3S_GN_TIMELINE")) {
+        if (tlv[0] == '1') {
+            ok = ok && cudaMalloc((void**)&p->timeline, sizeof(long long) * 8 * nblk) == cudaSuccess &&
+                 cudaMemset(p->timeline, 0, sizeof(long long) * 8 * nblk) == cudaSuccess;
+        }
+    }
     ok = ok && cudaMalloc((void**)&p->g, sizeof(double) * std::max(p->dim, 1)) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&p->dx, sizeof(double) * std::max(p->dim, 1)) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&p->status, sizeof(Status)) == cudaSuccess;
@@ -1193,6 +1424,10 @@ M3S_API double* m3s_gn_plan_H(m3s_gn_plan* plan) { return plan ? plan->Hm : null
 M3S_API double* m3s_gn_plan_g(m3s_gn_plan* plan) { return plan ? plan->g : nullptr; }
 M3S_API double* m3s_gn_plan_dx(m3s_gn_plan* plan) { return plan ? plan->dx : nullptr; }
 M3S_API double* m3s_gn_plan_poses(m3s_gn_plan* plan) { return plan ? plan->poses : nullptr; }
+M3S_API long long* m3s_gn_plan_timeline(m3s_gn_plan* plan, int64_t* count_out) {
+    if (count_out) *count_out = (plan && plan->timeline) ? 8LL * std::max(plan->np / kNB, 1) : 0;
+    return plan ? plan->timeline : nullptr;
+}
 
 M3S_API int m3s_gn_set_poses(m3s_gn_plan* plan, const float* Twc, m3s_stream_t stream) {
     M3S_REQUIRE(plan && Twc, "gn_set_poses: null pointer");
@@ -1297,6 +1532,7 @@ M3S_API int m3s_gn_assemble(m3s_gn_plan* plan, m3s_stream_t stream) {
     // NOTE: the memset is unconditional (cheap); kernels after a stop are no-ops and H is not
     // consumed any more.
     M3S_CUDA(cudaMemsetAsync(plan->Hm, 0, sizeof(double) * (size_t)(plan->np + 1) * plan->np, st));
+    M3S_CUDA(cudaMemsetAsync(plan->flags, 0, sizeof(int) * std::max(plan->np / kNB, 1), st));
     gn_assemble_kernel<<<plan->nblocks_H, 64, 0, st>>>(plan->status, plan->blocks, plan->list_edge,
                                                        plan->list_sign, plan->edge_blocks, plan->Hm,
                                                        plan->np, plan->dim, plan->g);
@@ -1308,22 +1544,24 @@ M3S_API int m3s_gn_assemble(m3s_gn_plan* plan, m3s_stream_t stream) {
     return M3S_OK;
 }
 
-// assemble + blocked Cholesky of the augmented matrix, enqueued on `st`
+// assemble + blocked Cholesky of the augmented matrix, enqueued on `st`: one launch per block step
 static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
     if (int rc = m3s_gn_assemble(plan, reinterpret_cast<m3s_stream_t>(st))) return rc;
     const int np = plan->np;
-    for (int k0 = 0; k0 < np; k0 += kNB) {
+    const int nblk = np / kNB;
+    chol_diag0_kernel<<<1, kStepThreads, 0, st>>>(plan->status, plan->Hm, plan->Lm, plan->Ldiag,
+                                                   plan->Linv, np, plan->timeline);
+    if (int rc = launch_ok("chol_diag0_kernel")) return rc;
+    for (int kb = 0; kb < nblk; ++kb) {
+        const int k0 = kb * kNB;
         const int rows_below = np + 1 - (k0 + kNB);  // incl. rhs row
-        const int grid = (rows_below + kTrsmRows - 1) / kTrsmRows + 1;  // + the inversion CTA
-        chol_panel_kernel<<<grid, kTrsmRows, 0, st>>>(plan->status, plan->Hm, plan->Ldiag, plan->Linv, np, k0);
-        if (int rc = launch_ok("chol_panel_kernel")) return rc;
         const int trailing = np - (k0 + kNB);
-        if (trailing > 0) {
-            const int tr = (rows_below + kSyrkTile - 1) / kSyrkTile;
-            const int tc = (trailing + kSyrkTile - 1) / kSyrkTile;
-            chol_syrk_kernel<<<dim3(tc, tr + 1), 256, 0, st>>>(plan->status, plan->Hm, plan->Ldiag, plan->Linv, np, k0);
-            if (int rc = launch_ok("chol_syrk_kernel")) return rc;
-        }
+        const int tr = (rows_below + kSyrkTile - 1) / kSyrkTile;
+        const int tc = std::max((trailing + kSyrkTile - 1) / kSyrkTile, 1);
+        chol_step_kernel<<<dim3(tc, tr + 2), kStepThreads, 0, st>>>(plan->status, plan->Hm, plan->Lm,
+                                                                   plan->Ldiag, plan->Linv, np, kb,
+                                                                   plan->timeline);
+        if (int rc = launch_ok("chol_step_kernel")) return rc;
     }
     return M3S_OK;
 }
@@ -1358,14 +1596,9 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
     } else {
         if (int rc = enqueue_assemble_factor(plan, st)) return rc;
     }
-    const size_t sh = sizeof(double) * np;
-    if (sh > 40 * 1024) {
-        M3S_CUDA(cudaFuncSetAttribute(gn_backsolve_update_kernel,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
-    }
-    gn_backsolve_update_kernel<<<1, kSolveThreads, sh, st>>>(plan->status, plan->Hm, plan->Linv, np,
-                                                            plan->dim, plan->F, plan->free_kf,
-                                                            gp->delta_thresh, plan->dx, plan->poses);
+    gn_backsolve_update_kernel<<<np / kNB, kBackThreads, 0, st>>>(
+        plan->status, plan->Lm, plan->Linv, np, plan->dim, plan->F, plan->free_kf, gp->delta_thresh,
+        plan->xsol, plan->flags, 1, plan->dx, plan->poses, plan->timeline);
     return launch_ok("gn_backsolve_update_kernel");
 }
 

@@ -1,0 +1,68 @@
+#!/usr/bin/env python
+"""Timeline of the 200-keyframe damped solve (dim 1393, 44 blocks of 32): per-kernel %globaltimer
+stamps of the two factorisation chains (diag / panel+syrk) and the dataflow back-substitution.
+    M3S_GN_TIMELINE=1 python scripts/gn_solve_timeline.py > gpurun_out/gn_timeline.txt
+"""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+os.environ["M3S_GN_TIMELINE"] = "1"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+from mast3r_slam_b200 import _lib, kernels as K, synth  # noqa: E402
+
+
+def main():
+    dev = torch.device("cuda", 0)
+    g = synth.make_graph(7, 200, 103, 48, 64, num_pts=512)
+    plan = K.GNPlan(g["ii"], g["jj"], 200, 512, 1, dev)
+    params = K.make_params(_lib.GN_POINTS, 1, 1, 0.0, 0.0, 1.5, 0.01)
+    t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a)).to(dev, dt)  # noqa: E731
+    Twc, Xs, Cs = t(g["Twc"], torch.float32), t(g["Xs"], torch.float32), t(g["Cs"], torch.float32)
+    idx, valid, Q = t(g["idx"], torch.int32), t(g["valid"].astype(np.uint8), torch.uint8), t(g["Q"], torch.float32)
+    lib = _lib.load()
+    p = lambda x: C.c_void_p(x.data_ptr())  # noqa: E731
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for rep in range(4):
+        _lib.check(lib.m3s_gn_set_poses(plan.handle, p(Twc), None))
+        _lib.check(lib.m3s_gn_accumulate(plan.handle, C.byref(params), p(Xs), p(Cs), p(idx), p(valid), p(Q),
+                                         0, plan.E, None))
+        torch.cuda.synchronize()
+        e0.record()
+        _lib.check(lib.m3s_gn_solve_update(plan.handle, C.byref(params), None))
+        e1.record()
+        torch.cuda.synchronize()
+    print(f"solve_update (assemble + factor + back-substitution + retract): {e0.elapsed_time(e1) * 1e3:.1f} us")
+    n = C.c_int64(0)
+    ptr = lib.m3s_gn_plan_timeline(plan.handle, C.byref(n))
+    assert ptr and n.value > 0, "timeline disabled"
+    iface = {"shape": (int(n.value),), "typestr": "<i8", "data": (int(ptr), False), "version": 3, "strides": None}
+    holder = type("_B", (), {"__cuda_array_interface__": iface})()
+    tl = torch.as_tensor(holder, device=dev).cpu().numpy().reshape(4, -1, 2).astype(np.float64)
+    nblk = tl.shape[1]
+    t0 = tl[tl > 0].min()
+    tl = (tl - t0) * 1e-3  # us
+    names = ["diag", "tile-solve", "tile-upd", "backsolve"]
+    for k, nm in enumerate(names):
+        d = tl[k]
+        ok = d[:, 1] > 0
+        dur = (d[ok, 1] - d[ok, 0])
+        print(f"{nm:9s}: n={ok.sum():3d} first start {d[ok, 0].min():8.1f} us, last end {d[ok, 1].max():8.1f} us, "
+              f"duration mean {dur.mean():6.2f} us (min {dur.min():.2f}, max {dur.max():.2f})")
+    print("step  diag[start end]      panel[start end]     syrk[start end]")
+    for kb in list(range(0, 6)) + list(range(20, 23)) + list(range(nblk - 3, nblk)):
+        print(f"{kb:4d}  " + "   ".join(f"{tl[k, kb, 0]:8.1f} {tl[k, kb, 1]:8.1f}" for k in range(3)))
+    per_step = (tl[1, nblk - 1, 1] - tl[0, 0, 0]) / nblk
+    print(f"factorisation: {tl[1, nblk - 1, 1] - tl[0, 0, 0]:.1f} us = {per_step:.2f} us per block step")
+    b = tl[3]
+    print(f"back-substitution: first CTA start {b[:, 0].min():.1f} us, block 0 published at {b[0, 1]:.1f} us "
+          f"({b[0, 1] - b[:, 0].min():.1f} us, {(b[0, 1] - b[nblk - 1, 1]) / max(nblk - 1, 1):.2f} us per block)")
+
+
+if __name__ == "__main__":
+    main()
