@@ -741,33 +741,51 @@ __device__ __forceinline__ double rsqrt_fast(double d) {
     return fma(y, e, y);
 }
 
-// 32x32 Cholesky by ONE warp, row `lane` of the block in registers; no shared memory and no
-// barrier on the 32-step dependent chain, so the whole factorisation is straight-line code the
-// scheduler can interleave.  Column j: the diagonal d_j and the entry a[j+1][j] are broadcast by
-// two independent shuffles, every lane derives rs = 1/sqrt(d_j) itself, scales its own entry
-// (l = a[j] rs) and updates the NEXT column first (a[j+1] -= l * a[j+1][j] rs: the only update the
-// next step waits for); the remaining columns follow with l broadcast from lane c by shuffle.
+// 32x32 Cholesky by ONE warp, row `lane` of the block in registers, no block barrier on the 32-step
+// dependent chain.  Column j:
+//   critical part (shuffles only): d_j and the entries a[j+1][j], a[j+2][j] are broadcast by three
+//     independent shuffles, every lane derives rs = 1/sqrt(d_j) itself, scales its own entry
+//     (l = a[j] rs) and updates the next TWO columns (a[j+1], a[j+2]) -- all the next two steps wait for;
+//   bulk part: the scaled column goes to a double-buffered 32-double shared array and the updates
+//     of columns >= j+3 are done one iteration LATER (all lanes read the same addresses: broadcast
+//     LDS.128), in the shadow of the next column's shuffle -> rsqrt -> scale latency.  One
+//     __syncwarp per column orders the shared-memory hand-over.
 // Entries above the diagonal pick up finite garbage that nothing reads.
-// (A block-wide version with one __syncthreads per column took 12 us per block, a warp version
-//  going through shared memory 8 us; measured with scripts/gn_solve_timeline.py.)
+// (Block-wide version with a __syncthreads per column: 12 us per block; all-shuffle warp version:
+//  ~5 us; measured with scripts/gn_solve_timeline.py.)
 __device__ __forceinline__ bool chol32_warp(double (*W)[kNB + 1], double (*L)[kNB + 1], double* dinv,
-                                            int lane) {
+                                            double (*col)[kNB], int lane) {
     double a[kNB];
 #pragma unroll
     for (int c = 0; c < kNB; ++c) a[c] = (c <= lane) ? W[lane][c] : 0.0;
     bool bad = false;
+    double lprev = 0.0;
 #pragma unroll
     for (int j = 0; j < kNB; ++j) {
         double d = __shfl_sync(0xffffffffu, a[j], j);
-        const double nxt = __shfl_sync(0xffffffffu, a[j], (j + 1) & 31);  // a[j+1][j]
-        if (!((d > 1e-290) && (d < 1e300))) { bad = true; d = 1.0; }      // warp-uniform
+        const double n1 = __shfl_sync(0xffffffffu, a[j], (j + 1) & 31);  // a[j+1][j]
+        const double n2 = __shfl_sync(0xffffffffu, a[j], (j + 2) & 31);  // a[j+2][j]
+        if (j > 0) {
+            // bulk update of column j-1 (columns >= j+2 of it; j+0, j+1 were done in its critical part)
+            const double2* cb = reinterpret_cast<const double2*>(col[(j - 1) & 1]);
+#pragma unroll
+            for (int c = j + 2; c < kNB; ++c) {
+                const double2 v = cb[c >> 1];
+                a[c] -= lprev * ((c & 1) ? v.y : v.x);
+            }
+        }
+        if (!((d > 1e-290) && (d < 1e300))) { bad = true; d = 1.0; }  // warp-uniform
         const double rs = rsqrt_fast(d);
         const double l = (lane == j) ? d * rs : a[j] * rs;
         a[j] = l;
         if (lane == j) dinv[j] = rs;
-        if (j + 1 < kNB) a[j + 1] -= l * (nxt * rs);
-#pragma unroll
-        for (int c = j + 2; c < kNB; ++c) a[c] -= l * __shfl_sync(0xffffffffu, l, c);
+        if (j + 1 < kNB) a[j + 1] -= l * (n1 * rs);
+        if (j + 2 < kNB) a[j + 2] -= l * (n2 * rs);
+        if (j + 3 < kNB) {
+            col[j & 1][lane] = l;
+            __syncwarp();
+        }
+        lprev = l;
     }
 #pragma unroll
     for (int c = 0; c < kNB; ++c) L[lane][c] = (c <= lane) ? a[c] : 0.0;
@@ -795,6 +813,7 @@ struct DiagSmem {
     double L[kNB][kNB + 1];   // previous factor, then this block's factor
     double Bm[kNB][kNB + 1];  // B = L[kb, kb-1]
     double dinv[kNB];
+    __align__(16) double col[2][kNB];  // chol32_warp's column hand-over
     int bad;
 };
 
@@ -853,7 +872,7 @@ __device__ __forceinline__ void chol_diag_block(DiagSmem& sm, Status* __restrict
     }
     __syncthreads();
     if (tid < 32) {
-        if (!chol32_warp(sm.W, sm.L, sm.dinv, tid) && tid == 0) sm.bad = 1;
+        if (!chol32_warp(sm.W, sm.L, sm.dinv, sm.col, tid) && tid == 0) sm.bad = 1;
     }
     __syncthreads();
     if (sm.bad) {
@@ -895,26 +914,26 @@ union StepSmem {
     DiagSmem d;
 };
 
-// grid = (max(#tile columns, 1), #tile rows + 2); blockIdx.y == #tile rows: CTA x == 0 inverts L_kb,
-// blockIdx.y == #tile rows + 1: CTA x == 0 is the diag CTA of block kb + 1.
-__global__ void __launch_bounds__(kStepThreads)
+// 1-D grid: block 0 = diag CTA of block kb + 1 (first, so it is dispatched first: it is the longest
+// CTA of the launch), block 1 inverts L_kb, blocks 2.. = the tiles of the trailing lower triangle,
+// row by row: tile rows 0 .. ntc-1 hold tr + 1 tiles each, a last tile row `ntc` (present when the
+// rhs row starts a new tile row) holds ntc tiles.
+__global__ void __launch_bounds__(kStepThreads, 2)  // 2 CTAs / SM: the 255 tiles of step 0 in one wave
 chol_step_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* __restrict__ Lm,
-                 double* __restrict__ Ldiag, double* __restrict__ Linv, int np, int kb,
+                 double* __restrict__ Ldiag, double* __restrict__ Linv, int np, int kb, int ntc,
                  long long* __restrict__ tl) {
     if (status->stopped | status->failed | status->chol_fail) return;
     __shared__ StepSmem sm;
     const int tid = threadIdx.x;
     const int nblk = np / kNB;
     const int k0 = kb * kNB;
-    const int ntr = (int)gridDim.y - 2;
-    const int tr = blockIdx.y, tc = blockIdx.x;
-    if (tr == ntr + 1) {
-        if (tc == 0 && kb + 1 < nblk) chol_diag_block(sm.d, status, Hm, Lm, Ldiag, Linv, np, kb + 1, tl);
+    if (blockIdx.x == 0) {
+        if (kb + 1 < nblk) chol_diag_block(sm.d, status, Hm, Lm, Ldiag, Linv, np, kb + 1, tl);
         return;
     }
-    if (tr == ntr) {
+    if (blockIdx.x == 1) {
         // invert L_kb for the back-substitution (the last block is inverted by its own diag CTA)
-        if (tc != 0 || kb == nblk - 1) return;
+        if (kb == nblk - 1) return;
         const double* Ld = Ldiag + (size_t)kb * kNB * kNB;
         for (int i = tid; i < kNB * kNB; i += kStepThreads) sm.t.D[i / kNB][i % kNB] = Ld[i];
         __syncthreads();
@@ -923,7 +942,20 @@ chol_step_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* _
         if (tid < 32) tri_inverse32(sm.t.D, sm.t.dinv, Linv + (size_t)kb * kNB * kNB, tid);
         return;
     }
-    if (tc > tr) return;
+    int tr, tc;
+    {
+        const int t = (int)blockIdx.x - 2;
+        const int ntri = ntc * (ntc + 1) / 2;
+        if (t >= ntri) {
+            tr = ntc;
+            tc = t - ntri;
+        } else {
+            tr = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
+            while (tr * (tr + 1) / 2 > t) --tr;
+            while ((tr + 1) * (tr + 2) / 2 <= t) ++tr;
+            tc = t - tr * (tr + 1) / 2;
+        }
+    }
     const bool first = (tr == 0) && (tc == 0);
     const bool stamp = (tl != nullptr) && first && (tid == 0);
     if (stamp) tl_stamp(tl, (1 * nblk + kb) * 2);
@@ -1556,11 +1588,13 @@ static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
         const int k0 = kb * kNB;
         const int rows_below = np + 1 - (k0 + kNB);  // incl. rhs row
         const int trailing = np - (k0 + kNB);
-        const int tr = (rows_below + kSyrkTile - 1) / kSyrkTile;
-        const int tc = std::max((trailing + kSyrkTile - 1) / kSyrkTile, 1);
-        chol_step_kernel<<<dim3(tc, tr + 2), kStepThreads, 0, st>>>(plan->status, plan->Hm, plan->Lm,
-                                                                   plan->Ldiag, plan->Linv, np, kb,
-                                                                   plan->timeline);
+        const int ntr = (rows_below + kSyrkTile - 1) / kSyrkTile;
+        const int ntc = (trailing + kSyrkTile - 1) / kSyrkTile;
+        // trailing == 0 (last step): one tile that only solves the rhs row
+        const int ntiles = (ntc == 0) ? 1 : ntc * (ntc + 1) / 2 + ((ntr > ntc) ? ntc : 0);
+        chol_step_kernel<<<2 + ntiles, kStepThreads, 0, st>>>(plan->status, plan->Hm, plan->Lm,
+                                                             plan->Ldiag, plan->Linv, np, kb,
+                                                             std::max(ntc, 1), plan->timeline);
         if (int rc = launch_ok("chol_step_kernel")) return rc;
     }
     return M3S_OK;
