@@ -240,6 +240,52 @@ int m3s_gauss_newton(m3s_gn_plan* plan, const m3s_gn_params* params, const float
                      const float* Xs, const float* Cs, const int32_t* idx, const uint8_t* valid,
                      const float* Q, float* Twc_out, m3s_stream_t stream);
 
+/* ---- tracker single-pose solves ------------------------------------------ */
+
+#define M3S_TRACK_RAY_DIST 0 /* FrameTracker._opt_pose_ray_dist_sim3 (tracker.py:255-313) */
+#define M3S_TRACK_CALIB 1    /* FrameTracker._opt_pose_calib_sim3    (tracker.py:315-406) */
+
+/* config "tracking" section (config.py:74-91) as it reaches the solver */
+typedef struct m3s_track_params {
+    int32_t mode;          /* M3S_TRACK_* */
+    int32_t max_iters;     /* 10 */
+    int32_t img_w, img_h;  /* calib only; img_w * img_h == N (pixel n = (n % img_w, n / img_w)) */
+    int32_t pixel_border;  /* calib only */
+    int32_t reserved;
+    double sigma_ray, sigma_dist;    /* 0.003, 10 */
+    double sigma_pixel, sigma_depth; /* 1, 10 */
+    double huber;                    /* 1.345 */
+    double rel_error, delta_norm;    /* 1e-3, 1e-3 (optimizer.py:11-46) */
+    double depth_eps;                /* calib only */
+    float K4[4];                     /* fx, fy, cx, cy (calib only) */
+} m3s_track_params;
+
+/* Replaces the confidence / mask block of FrameTracker.track (tracker.py:86-113):
+ *   Qk = sqrt(Qff[idx] * Qkf); valid_kf = valid_match & (Qk > Q_conf);
+ *   valid_opt = valid_kf & (Cf[idx] > C_conf) & (Ck > C_conf); counts_out = {sum valid_opt, sum valid_kf}.
+ * All arrays [N] on the device (Cf, Qff indexed through idx_f2k). */
+int m3s_track_gate(const float* Cf, const float* Ck, const float* Qff, const float* Qkf,
+                   const int32_t* idx_f2k, const uint8_t* valid_match, float C_conf, float Q_conf,
+                   float* Qk_out, uint8_t* valid_opt_out, uint8_t* valid_kf_out,
+                   int32_t* counts_out, int N, m3s_stream_t stream);
+
+size_t m3s_track_workspace_bytes(int N);
+
+/* Replaces FrameTracker._opt_pose_ray_dist_sim3 / _opt_pose_calib_sim3 incl. _solve (tracker.py:216-253),
+ * point_to_ray_dist / act_Sim3 / project_calib Jacobians (geometry.py:46-227), Sim3.retr and
+ * check_convergence (optimizer.py:11-46).  The whole <= max_iters loop is enqueued without host
+ * synchronisation (a device flag replays the reference's `break`).
+ *   Xf [N,3] frame points; idx_f2k [N] i32 gathers them (Xf[idx_f2k], tracker.py:214) or NULL if the
+ *   caller already gathered; Xk [N,3] keyframe points; Qk [N]; valid [N] u8 (valid_opt; in calib
+ *   mode the measurement / projection masks are derived from Xk and the projected point);
+ *   T_WCf, T_WCk [8] f32 device (t, q_xyzw, s) -> T_WCf_out, T_CkCf_out [8] f32 device;
+ *   stats_out (device, may be NULL) = {iterations done, last cost, last |tau|, 1 if the solve failed}. */
+int m3s_track_opt_pose(const m3s_track_params* params, const float* Xf, const int32_t* idx_f2k,
+                       const float* Xk, const float* Qk, const uint8_t* valid, int N,
+                       const float* T_WCf, const float* T_WCk, float* T_WCf_out, float* T_CkCf_out,
+                       double* stats_out, void* workspace, size_t workspace_bytes,
+                       m3s_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -24,6 +24,7 @@ SOURCES = {
     "gn.cu": [],
     "graph_host.cu": ["-fmad=false"],
     "host_pipeline.cu": [],
+    "track.cu": ["-fmad=false"],
 }
 
 

@@ -28,6 +28,20 @@ class GNParams(C.Structure):
     ]
 
 
+TRACK_RAY_DIST, TRACK_CALIB = 0, 1
+
+
+class TrackParams(C.Structure):
+    """struct m3s_track_params (include/m3s.h)."""
+    _fields_ = [
+        ("mode", C.c_int32), ("max_iters", C.c_int32), ("img_w", C.c_int32), ("img_h", C.c_int32),
+        ("pixel_border", C.c_int32), ("reserved", C.c_int32),
+        ("sigma_ray", C.c_double), ("sigma_dist", C.c_double), ("sigma_pixel", C.c_double),
+        ("sigma_depth", C.c_double), ("huber", C.c_double), ("rel_error", C.c_double),
+        ("delta_norm", C.c_double), ("depth_eps", C.c_double), ("K4", C.c_float * 4),
+    ]
+
+
 _vp, _i, _f, _sz, _i64 = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_int64
 
 # name -> (restype, argtypes); every symbol include/m3s.h declares
@@ -50,6 +64,10 @@ SIGNATURES = {
     "m3s_match_host_release": (_i, [_i]),
     "m3s_constrain_points_to_ray": (_i, [_vp, C.POINTER(C.c_float), _vp, _i, _i, _i, _vp]),
     "m3s_edge_confidence": (_i, [_vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _i, C.c_longlong, _vp]),
+    "m3s_track_gate": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _i, _vp]),
+    "m3s_track_workspace_bytes": (_sz, [_i]),
+    "m3s_track_opt_pose": (_i, [C.POINTER(TrackParams), _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp,
+                                _vp, _vp, _sz, _vp]),
     "m3s_gn_plan_create": (_vp, [_vp, _vp, _i, _i, _i64, _i, _i]),
     "m3s_gn_plan_destroy": (None, [_vp]),
     "m3s_gn_plan_num_free": (_i, [_vp]),

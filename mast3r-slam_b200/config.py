@@ -22,6 +22,12 @@ DEFAULT_CONFIG = {
         "refine_dilation": 2,        # matching.py:406
         "use_refine": True,          # matching.py:407
     },
+    "tracking": {                    # config.py:74-91
+        "min_match_frac": 0.05, "C_conf": 0.0, "Q_conf": 1.5, "rel_error": 1e-3, "delta_norm": 1e-3,
+        "max_iters": 10, "huber": 1.345, "sigma_ray": 0.003, "sigma_dist": 10.0, "sigma_pixel": 1.0,
+        "sigma_depth": 10.0, "pixel_border": 0, "depth_eps": 0.0, "match_frac_thresh": 0.333,
+        "use_calib": False,
+    },
     "local_opt": {
         "pin": 1, "max_iters": 10, "C_conf": 0.0, "Q_conf": 1.5, "sigma_ray": 0.003,
         "sigma_dist": 10.0, "sigma_pixel": 1.0, "sigma_depth": 10.0, "pixel_border": 0,

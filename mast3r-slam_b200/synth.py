@@ -199,6 +199,22 @@ def make_graph(seed: int = 0, num_kf: int = 10, num_loops: int = 3, h: int = 384
                 jj=jj, idx=idx, valid=valid, Q=Q, K4=K4, img_size=(w, h))
 
 
+def make_track_pair(seed: int = 0, h: int = 384, w: int = 512, num_pts: int | None = None,
+                    noise: float = 1e-3, valid_frac: float = 0.85):
+    """Tracking problem (tracker.py:51-180): keyframe = KF 0 of `make_graph` (exact pose, its points
+    sit on its own pixel grid), frame = KF 1 (perturbed pose, points in shifted order).  Returns
+    dict(Xf, Xk [N,3], idx_f2k [N] i32 (keyframe pixel n <-> frame point idx_f2k[n]), valid_match
+    [N,1] bool, Cf, Ck [N], Qff, Qkf [N], T_WCf (perturbed), T_WCf_gt, T_WCk [8], K4, img_size (h,w))."""
+    g = make_graph(seed, 2, 0, h, w, num_pts, noise, valid_frac=valid_frac)
+    assert (g["ii"][1], g["jj"][1]) == (1, 0)
+    rng = np.random.default_rng(9000 + seed)
+    n = g["Xs"].shape[1]
+    return dict(Xf=g["Xs"][1], Xk=g["Xs"][0], idx_f2k=g["idx"][1], valid_match=g["valid"][1][:, None],
+                Cf=g["Cs"][1], Ck=g["Cs"][0], Qff=rng.uniform(1.2, 4.0, n).astype(np.float32),
+                Qkf=rng.uniform(1.2, 4.0, n).astype(np.float32), T_WCf=g["Twc"][1],
+                T_WCf_gt=g["Twc_gt"][1], T_WCk=g["Twc"][0], K4=g["K4"], img_size=(h, w))
+
+
 # ---------------------------------------------------------------------------------------------
 # value distributions of the reference's own benchmark generators (incoherent worst cases)
 # ---------------------------------------------------------------------------------------------

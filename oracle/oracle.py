@@ -293,3 +293,203 @@ def add_factors_numpy(ii, jj, match_out, Q_conf, min_match_frac, is_reloc=False)
     if keep.sum() == 0:
         return None
     return (ii_t[keep], jj_t[keep], idx_i2j[keep], idx_j2i[keep], vmj[keep], vmi[keep], Qj[keep], Qi[keep])
+
+
+# ---------------------------------------------------------------------------------------------
+# Tracker single-pose solves.  numpy restatement of tracker.py:216-406,
+# geometry.py:46-227, liegroups/{so3,sim3}.py and optimizer.py:11-62.  The reference evaluates
+# these in MLX (not importable here: parity UNPINNED for this row -- restated, never executed);
+# `dtype` selects the arithmetic (float64 = the exact-math statement the CUDA path is checked
+# against, float32 = the reference's own precision, used to size the tolerance).
+# ---------------------------------------------------------------------------------------------
+def _cross(a, b):  # liegroups/so3.py:9-25
+    return np.stack([a[..., 1] * b[..., 2] - a[..., 2] * b[..., 1],
+                     a[..., 2] * b[..., 0] - a[..., 0] * b[..., 2],
+                     a[..., 0] * b[..., 1] - a[..., 1] * b[..., 0]], axis=-1)
+
+
+def _so3_act(q, p):  # so3.py:147-167
+    t = 2.0 * _cross(q[..., :3], p)
+    return p + q[..., 3:4] * t + _cross(q[..., :3], t)
+
+
+def _so3_mul(q1, q2):  # so3.py:125-145
+    x1, y1, z1, w1 = q1
+    x2, y2, z2, w2 = q2
+    return np.array([w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2, w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2,
+                     w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2, w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2],
+                    dtype=q1.dtype)
+
+
+def _sim3_mul(a, b):  # sim3.py:206-220
+    t = a[:3] + a[7] * _so3_act(a[3:7], b[:3])
+    return np.concatenate([t, _so3_mul(a[3:7], b[3:7]), [a[7] * b[7]]]).astype(a.dtype)
+
+
+def _sim3_inv(a):  # sim3.py:195-204
+    qi = np.concatenate([-a[3:6], a[6:7]])
+    si = 1.0 / (a[7] + a.dtype.type(1e-10))
+    return np.concatenate([-si * _so3_act(qi, a[:3]), qi, [si]]).astype(a.dtype)
+
+
+def _sim3_exp(tau):  # sim3.py:106-154 + so3.py:65-96
+    dt = tau.dtype.type
+    v, w, sigma = tau[:3], tau[3:6], tau[6]
+    th2 = np.sum(w * w)
+    th = np.sqrt(th2 + dt(1e-10))
+    small = th2 < 1e-8
+    with np.errstate(all="ignore"):
+        A = dt(1.0) - th2 / dt(6.0) if small else np.sin(th) / th
+        B = dt(0.5) - th2 / dt(24.0) if small else (dt(1.0) - np.cos(th)) / th2
+        Cc = dt(1.0 / 6.0) - th2 / dt(120.0) if small else (dt(1.0) - A) / th2
+        wv = _cross(w, v)
+        t = v + B * wv + Cc * _cross(w, wv)
+        half = dt(0.5) * th
+        sh = dt(0.5) - th2 / dt(48.0) if small else np.sin(half) / th
+        ch = dt(1.0) - th2 / dt(8.0) if small else np.cos(half)
+    return np.concatenate([t, sh * w, [ch], [np.exp(sigma)]]).astype(tau.dtype)
+
+
+def _track_solve(sqrt_info, r, J, huber):  # tracker.py:216-253
+    wr = np.abs(sqrt_info * r)
+    with np.errstate(all="ignore"):
+        hw = np.where(wr < huber, np.ones_like(wr), huber / wr)
+    rs = sqrt_info * np.sqrt(hw)
+    m = J.shape[-1]
+    A = (rs[..., None] * J).reshape(-1, m)
+    b = (rs * r).reshape(-1, 1)
+    H = A.T @ A
+    g = -(A.T @ b)
+    cost = 0.5 * float((b.T @ b).item())
+    tau = np.linalg.solve(H + 1e-6 * np.eye(m, dtype=H.dtype), g[:, 0])  # linalg.py:17-50
+    return tau.astype(J.dtype), cost
+
+
+def _converged(rel_thr, dn_thr, old, new, tau):  # optimizer.py:11-46
+    with np.errstate(all="ignore"):
+        rel = abs(np.float64(old - new) / np.float64(old + 1e-10))
+    dn = float(np.sqrt(np.sum(tau.astype(np.float64) ** 2)))
+    return bool(rel < rel_thr or dn < dn_thr)
+
+
+def _act_jac(T, X):  # geometry.py:95-137
+    pW = T[7] * _so3_act(T[3:7][None], X) + T[:3]
+    n = pW.shape[0]
+    J = np.zeros((n, 3, 7), dtype=pW.dtype)
+    J[:, 0, 0] = J[:, 1, 1] = J[:, 2, 2] = 1.0
+    x, y, z = pW[:, 0], pW[:, 1], pW[:, 2]
+    J[:, 0, 4], J[:, 0, 5] = z, -y          # -skew(pW)
+    J[:, 1, 3], J[:, 1, 5] = -z, x
+    J[:, 2, 3], J[:, 2, 4] = y, -x
+    J[:, :, 6] = pW
+    return pW, J
+
+
+def _ray_dist(X, jac):  # geometry.py:46-92
+    d = np.sqrt(np.sum(X * X, axis=-1, keepdims=True) + X.dtype.type(1e-10))
+    di = 1.0 / d
+    r = di * X
+    rd = np.concatenate([r, d], axis=-1)
+    if not jac:
+        return rd
+    eye = np.eye(3, dtype=X.dtype)[None]
+    dr = di[:, :, None] * (eye - (di ** 2)[:, :, None] * (X[:, :, None] @ X[:, None, :]))
+    return rd, np.concatenate([dr, r[:, None, :]], axis=1)
+
+
+DEFAULT_TRACKING = {"C_conf": 0.0, "Q_conf": 1.5, "rel_error": 1e-3, "delta_norm": 1e-3,
+                    "max_iters": 10, "huber": 1.345, "sigma_ray": 0.003, "sigma_dist": 10.0,
+                    "sigma_pixel": 1.0, "sigma_depth": 10.0, "pixel_border": 0, "depth_eps": 0.0}
+
+
+def opt_pose_ray_dist_sim3_numpy(Xf, Xk, T_WCf, T_WCk, Qk, valid, cfg=None, dtype=np.float64):
+    """tracker.py:255-313.  Returns (T_WCf, T_CkCf, info)."""
+    cfg = {**DEFAULT_TRACKING, **(cfg or {})}
+    Xf, Xk = np.asarray(Xf, dtype).reshape(-1, 3), np.asarray(Xk, dtype).reshape(-1, 3)
+    Qk = np.asarray(Qk, dtype).reshape(-1, 1)
+    vf = np.asarray(valid).reshape(-1, 1).astype(dtype)
+    Tf, Tk = np.asarray(T_WCf, dtype).reshape(8), np.asarray(T_WCk, dtype).reshape(8)
+    si_ray = dtype(1.0 / cfg["sigma_ray"]) * vf * np.sqrt(Qk)
+    si_dist = dtype(1.0 / cfg["sigma_dist"]) * vf * np.sqrt(Qk)
+    sqrt_info = np.concatenate([np.broadcast_to(si_ray, (len(Qk), 3)), si_dist], axis=-1)
+    T = _sim3_mul(_sim3_inv(Tk), Tf)
+    rd_k = _ray_dist(Xk, False)
+    old, it, cost = float("inf"), 0, 0.0
+    for _ in range(cfg["max_iters"]):
+        pW, dX = _act_jac(T, Xf)
+        rd_f, drd = _ray_dist(pW, True)
+        r = rd_k - rd_f
+        J = -(drd @ dX)
+        tau, cost = _track_solve(sqrt_info, r, J, dtype(cfg["huber"]))
+        T = _sim3_mul(T, _sim3_exp(tau))
+        it += 1
+        if _converged(cfg["rel_error"], cfg["delta_norm"], old, cost, tau):
+            break
+        old = cost
+    return _sim3_mul(Tk, T), T, {"iterations": it, "cost": cost,
+                                 "delta_norm": float(np.linalg.norm(tau)) if it else 0.0}
+
+
+def opt_pose_calib_sim3_numpy(Xf, Xk, T_WCf, T_WCk, Qk, valid, K, img_size, cfg=None, dtype=np.float64):
+    """tracker.py:315-406 with meas_k / valid_meas_k from _get_points_poses (:195-212) and
+    project_calib (geometry.py:155-227).  img_size = (h, w); K = 3x3 or (fx,fy,cx,cy)."""
+    cfg = {**DEFAULT_TRACKING, **(cfg or {})}
+    K = np.asarray(K, dtype)
+    fx, fy, cx, cy = (K[0, 0], K[1, 1], K[0, 2], K[1, 2]) if K.shape == (3, 3) else K
+    h, w = int(img_size[0]), int(img_size[1])
+    Xf, Xk = np.asarray(Xf, dtype).reshape(-1, 3), np.asarray(Xk, dtype).reshape(-1, 3)
+    n = len(Xk)
+    Qk = np.asarray(Qk, dtype).reshape(-1, 1)
+    vf = np.asarray(valid).reshape(-1, 1).astype(dtype)
+    Tf, Tk = np.asarray(T_WCf, dtype).reshape(8), np.asarray(T_WCk, dtype).reshape(8)
+    border, z_eps = cfg["pixel_border"], cfg["depth_eps"]
+    lin = np.arange(n)
+    with np.errstate(all="ignore"):
+        meas = np.stack([(lin % w).astype(dtype), (lin // w).astype(dtype),
+                         np.log(Xk[:, 2] + dtype(1e-10))], axis=-1)
+    vmeas = Xk[:, 2:3] > z_eps
+    meas = np.where(vmeas, meas, 0)
+    si_px = dtype(1.0 / cfg["sigma_pixel"]) * vf * np.sqrt(Qk)
+    si_z = dtype(1.0 / cfg["sigma_depth"]) * vf * np.sqrt(Qk)
+    sqrt_info = np.concatenate([np.broadcast_to(si_px, (n, 2)), si_z], axis=-1)
+    T = _sim3_mul(_sim3_inv(Tk), Tf)
+    old, it, cost = float("inf"), 0, 0.0
+    for _ in range(cfg["max_iters"]):
+        P, dX = _act_jac(T, Xf)
+        x, y, z = P[:, 0], P[:, 1], P[:, 2]
+        with np.errstate(all="ignore"):
+            zden = z + dtype(1e-10)
+            u, v = (fx * x + cx * z) / zden, (fy * y + cy * z) / zden
+            vz = z > z_eps
+            vproj = (u > border) & (u < w - 1 - border) & (v > border) & (v < h - 1 - border) & vz
+            logz = np.where(vz, np.log(z + dtype(1e-10)), 0)
+            zi = 1.0 / zden
+        dpz = np.zeros((n, 3, 3), dtype=dtype)
+        dpz[:, 0, 0], dpz[:, 0, 2] = fx * zi, -fx * x * zi * zi
+        dpz[:, 1, 1], dpz[:, 1, 2] = fy * zi, -fy * y * zi * zi
+        dpz[:, 2, 2] = zi
+        v2 = (vproj[:, None] & vmeas)
+        si2 = np.where(v2, sqrt_info, 0)
+        r = np.where(v2, meas - np.stack([u, v, logz], axis=-1), 0)   # masked rows carry weight 0
+        J = np.where(v2[..., None], -(dpz @ dX), 0)
+        tau, cost = _track_solve(si2, r, J, dtype(cfg["huber"]))
+        T = _sim3_mul(T, _sim3_exp(tau))
+        it += 1
+        if _converged(cfg["rel_error"], cfg["delta_norm"], old, cost, tau):
+            break
+        old = cost
+    return _sim3_mul(Tk, T), T, {"iterations": it, "cost": cost,
+                                 "delta_norm": float(np.linalg.norm(tau)) if it else 0.0}
+
+
+def track_gate_numpy(Cf, Ck, Qff, Qkf, idx_f2k, valid_match_k, C_conf=0.0, Q_conf=1.5):
+    """tracker.py:86-113 in float32."""
+    idx = np.asarray(idx_f2k).reshape(-1)
+    Cf, Ck = _f32(Cf).reshape(-1), _f32(Ck).reshape(-1)
+    Qff, Qkf = _f32(Qff).reshape(-1), _f32(Qkf).reshape(-1)
+    vm = np.asarray(valid_match_k).reshape(-1).astype(bool)
+    Qk = np.sqrt(Qff[idx] * Qkf)
+    v_q = Qk > np.float32(Q_conf)
+    v_opt = vm & (Cf[idx] > np.float32(C_conf)) & (Ck > np.float32(C_conf)) & v_q
+    v_kf = vm & v_q
+    return Qk[:, None], v_opt[:, None], v_kf[:, None], (int(v_opt.sum()), int(v_kf.sum()))
