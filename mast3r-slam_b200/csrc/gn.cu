@@ -487,6 +487,55 @@ gn_accum_mixed_kernel(const Status* __restrict__ status, KernelParams P,
         const float4* __restrict__ c4p = reinterpret_cast<const float4*>(Cj);
         const float4* __restrict__ x4p = reinterpret_cast<const float4*>(Xj);
         const int Ni = (int)N;  // vec path is only taken for N < 2^31 (host check)
+#ifndef M3S_ACCF_NO_PREFETCH  // default; the plain loop below is kept for A/B runs (B200: 1.38 -> 1.34 ms)
+        // Two-stage software pipeline: the seven streaming vector loads of trip t+1 are issued before
+        // the gathers and the arithmetic of trip t, so only the (idx-dependent) gather latency is
+        // exposed per trip instead of stream + gather back to back.
+        const int g_end = (int)(n1 >> 2);
+        int g = (int)(n0 >> 2) + threadIdx.x;
+        uchar4 v4 = make_uchar4(0, 0, 0, 0);
+        float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f), c4 = q4, xa = q4, xb = q4, xc = q4;
+        int4 i4 = make_int4(0, 0, 0, 0);
+        if (g < g_end) {
+            v4 = __ldg(v4p + g); q4 = __ldg(q4p + g); i4 = __ldg(i4p + g); c4 = __ldg(c4p + g);
+            xa = __ldg(x4p + 3 * g); xb = __ldg(x4p + 3 * g + 1); xc = __ldg(x4p + 3 * g + 2);
+        }
+        for (; g < g_end; g += kAccThreads) {
+            const unsigned char vv[4] = {v4.x, v4.y, v4.z, v4.w};
+            const float qq[4] = {q4.x, q4.y, q4.z, q4.w};
+            const int ii4[4] = {i4.x, i4.y, i4.z, i4.w};
+            const float cc[4] = {c4.x, c4.y, c4.z, c4.w};
+            const float xj[4][3] = {{xa.x, xa.y, xa.z}, {xa.w, xb.x, xb.y}, {xb.z, xb.w, xc.x}, {xc.y, xc.z, xc.w}};
+            bool okp[4];
+            float ci[4], xi[4][3];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                int m = ii4[u];
+                m += (m < 0) ? Ni : 0;  // numpy negative indexing (gauss_newton.py:125)
+                okp[u] = vv[u] && ((unsigned)m < (unsigned)Ni) && (qq[u] > P.q_th) && (cc[u] > P.c_th);
+                m = okp[u] ? m : 0;
+                ci[u] = __ldg(Ci + m);
+                const float* __restrict__ xp = Xi + 3 * (size_t)(unsigned)m;
+                xi[u][0] = __ldg(xp); xi[u][1] = __ldg(xp + 1); xi[u][2] = __ldg(xp + 2);
+            }
+            const int gn = g + kAccThreads;
+            if (gn < g_end) {
+                v4 = __ldg(v4p + gn); q4 = __ldg(q4p + gn); i4 = __ldg(i4p + gn); c4 = __ldg(c4p + gn);
+                xa = __ldg(x4p + 3 * gn); xb = __ldg(x4p + 3 * gn + 1); xc = __ldg(x4p + 3 * gn + 2);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (okp[u] && (ci[u] > P.c_th))
+                    accumulate_point_f32<MODE>(P, ec, xj[u][0], xj[u][1], xj[u][2], xi[u][0], xi[u][1],
+                                               xi[u][2], qq[u], acc);
+            }
+        }
+#else
+#ifndef M3S_ACCF_UNROLL
+#define M3S_ACCF_UNROLL 1
+#endif
+        constexpr int kTripUnroll = M3S_ACCF_UNROLL;
+#pragma unroll kTripUnroll
         for (int g = (int)(n0 >> 2) + threadIdx.x; g < (int)(n1 >> 2); g += kAccThreads) {
             const uchar4 v4 = __ldg(v4p + g);
             const float4 q4 = __ldg(q4p + g);
@@ -517,6 +566,7 @@ gn_accum_mixed_kernel(const Status* __restrict__ status, KernelParams P,
                                                xi[u][2], qq[u], acc);
             }
         }
+#endif
     } else {
         for (long long n = n0 + threadIdx.x; n < n1; n += kAccThreads) {
             if (!__ldg(ve + n)) continue;
@@ -1388,14 +1438,19 @@ M3S_API m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii, const int32_t* jj, in
     }
     p->nblocks_H = (int)blocks.size();
 
-    // chunking of the point dimension: aim for >= ~6 CTAs per SM in flight, 1024..8192 pts/CTA
+    // chunking of the point dimension: aim for >= ~6 CTAs per SM in flight, 1024..32768 pts/CTA
+    // (B200, 1000 edges x 196608 pts: 8192 -> 1.56 ms, 16384 -> 1.43, 32768 -> 1.38, 65536 -> 1.39:
+    // the per-CTA prologue (relative pose in fp64) and the fp64 block reduction amortise)
     {
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         const long long target_blocks = 6LL * sms;
         long long nch = (n_active > 0) ? (target_blocks + n_active - 1) / n_active : 1;
         const long long max_ch = std::max<long long>(1, (N + 1023) / 1024);
-        const long long min_ch = std::max<long long>(1, (N + 8191) / 8192);
+#ifndef M3S_ACC_MAX_CHUNK
+#define M3S_ACC_MAX_CHUNK 32768
+#endif
+        const long long min_ch = std::max<long long>(1, (N + M3S_ACC_MAX_CHUNK - 1) / M3S_ACC_MAX_CHUNK);
         nch = std::min(std::max(nch, min_ch), max_ch);
         long long cp = (N + nch - 1) / std::max<long long>(nch, 1);
         cp = std::max<long long>(((cp + kAccThreads - 1) / kAccThreads) * kAccThreads, kAccThreads);
