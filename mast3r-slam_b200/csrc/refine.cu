@@ -311,15 +311,22 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
         const bool in0 = (wx0 + px0 >= 0) && (wx0 + px0 < W);
         const bool in1 = (f1 < ROW4) && (wx0 + px1 >= 0) && (wx0 + px1 < W);
         const int s0 = px0 * P4 + (f0 - px0 * D4), s1 = px1 * P4 + (f1 - px1 * D4);
+        // hoisted addressing: one 64-bit source pointer and one 32-bit shared address per copy,
+        // advanced by constant strides; only rows inside the image are visited (the per-row
+        // address arithmetic of the first version was 11 % of all executed instructions, ncu s15)
+        const int wy_lo = max(0, -wy0), wy_hi = min(kWinY, H - wy0);
+        const size_t grow = (size_t)W * D4;  // float4 per image row
+        // `src` may point before the row start when wx0 < 0; only in-image elements are touched
+        const float4* __restrict__ src = img + ((long long)(wy0 + wy_lo) * W + wx0) * D4;
+        unsigned d0 = (unsigned)__cvta_generic_to_shared(tile + wy_lo * kWinX * P4 + s0);
+        const unsigned d10 = (unsigned)((s1 - s0) * 16);
+        constexpr unsigned srow = kWinX * P4 * 16;
 #pragma unroll 4
-        for (int wy = 0; wy < kWinY; ++wy) {
-            const int gy = wy0 + wy;
-            if (gy < 0 || gy >= H) continue;
-            // `src` may point before the row start when wx0 < 0; only in-image elements are touched
-            const float4* __restrict__ src = img + ((long long)gy * W + wx0) * D4;
-            float4* dst = tile + wy * kWinX * P4;
-            if (in0) cp_async16(dst + s0, src + f0);
-            if (in1) cp_async16(dst + s1, src + f1);
+        for (int wy = wy_lo; wy < wy_hi; ++wy) {
+            if (in0) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d0), "l"(src + f0) : "memory");
+            if (in1) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d0 + d10), "l"(src + f1) : "memory");
+            src += grow;
+            d0 += srow;
         }
     }
     float4 q[kQ][D4];

@@ -37,6 +37,13 @@ for r in rows[2:]:
         pass
 tots = sum(d[0] for d in data) or 1
 print(f'total samples {tots}, SASS instructions {len(data)}, warp-instr executed {sum(d[1] for d in data)}')
+ops = {}
+for s_, e, text, r in data:
+    t = text.split()
+    op = (t[1] if t and t[0].startswith('@') and len(t) > 1 else (t[0] if t else '?')).split('.')[0]
+    ops[op] = ops.get(op, 0) + e
+te = sum(ops.values()) or 1
+print('dynamic opcode mix:', ', '.join(f'{k} {100*x/te:.1f}%' for k, x in sorted(ops.items(), key=lambda kv: -kv[1])[:14]))
 for s, e, text, r in sorted(data, key=lambda d: -d[0])[:topn]:
     sts = {hdr[k].replace('stall_', ''): r[k] for k in range(len(hdr)) if hdr[k].startswith('stall_') and '(' not in hdr[k] and r[k] not in ('0', '')}
     top = sorted(sts.items(), key=lambda kv: -int(kv[1]))[:2]
