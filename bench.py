@@ -323,6 +323,10 @@ def main():
                                                 "solve_update_ms", "roofline", "status", "precision")}
         gn.pop("_poses", None)
 
+    track = None
+    if rank == 0 and not args.no_gn:
+        track = track_leg(dev)
+
     if rank == 0:
         line = {
             "metric": "matched_px_per_s (iter_proj+refine_matches, 512x384, D=24, 10 it, r=3)",
@@ -336,7 +340,7 @@ def main():
                        "l2_policy": "inputs larger than L2 (3.1 GB per step vs 126 MB L2)",
                        "parallelism": f"pairs x{world} (no collective)"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": 4 * args.steps, "roofline": roofline,
-            "cpu_baseline": cpu_baseline, "gn": gn, "wall_s_timed_region": round(t_wall, 4),
+            "cpu_baseline": cpu_baseline, "gn": gn, "track": track, "wall_s_timed_region": round(t_wall, 4),
         }
         print(json.dumps(line))
     if world > 1:
@@ -420,6 +424,39 @@ def gn_leg(args, rank, world, dev, peak, precision):
     }
 
 
+def track_leg(dev):
+    """one frame-to-keyframe Sim3 solve (tracker.py:255-406) at 512x384, inputs resident
+    on the device, event-timed over 20 solves (each = init + up to 10 x (accumulate + solve))."""
+    import torch
+    from mast3r_slam_b200 import synth, tracker
+    d = synth.make_track_pair(0, H, W)
+    t = lambda a, dt=torch.float32: torch.from_numpy(a).to(dev, dt)  # noqa: E731
+    Qk, v_opt, _, (n_opt, _) = tracker.track_gate(t(d["Cf"]), t(d["Ck"]), t(d["Qff"]), t(d["Qkf"]),
+                                                  t(d["idx_f2k"], torch.int32),
+                                                  t(d["valid_match"].astype("uint8"), torch.uint8))
+    Xf, Xk, idx = t(d["Xf"]), t(d["Xk"]), t(d["idx_f2k"], torch.int32)
+    Tf, Tk = t(d["T_WCf"]), t(d["T_WCk"])
+    out = {}
+    for name, fn in (("ray_dist", lambda: tracker.opt_pose_ray_dist_sim3(Xf, Xk, Tf, Tk, Qk, v_opt, idx_f2k=idx)),
+                     ("calib", lambda: tracker.opt_pose_calib_sim3(Xf, Xk, Tf, Tk, Qk, v_opt, d["K4"], (H, W),
+                                                                    idx_f2k=idx))):
+        for _ in range(3):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(20):
+            res = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        out[name] = {"ms_per_solve": round(e0.elapsed_time(e1) / 20, 4),
+                     "pose_err_after": float((res[0].cpu() - torch.from_numpy(d["T_WCf_gt"])).abs().max())}
+    out["points"] = NPIX
+    out["valid_points"] = n_opt
+    out["pose_err_before"] = float(abs(d["T_WCf"] - d["T_WCf_gt"]).max())
+    return out
+
+
 def reference_arm(args, rank, world):
     """The reference's own CPU implementation of the path (its numpy fallbacks, which is what its
     dispatcher executes without Metal), as the C/OpenMP port in oracle/ on all host threads.  The
@@ -432,6 +469,12 @@ def reference_arm(args, rank, world):
     from mast3r_slam_b200 import synth
     from oracle import oracle
     oracle.build()
+    # torchrun exports OMP_NUM_THREADS=1 for every rank; the reference arm is a CPU measurement and
+    # uses every host core this process may run on
+    try:
+        oracle.set_threads(len(os.sched_getaffinity(0)))
+    except Exception:
+        oracle.set_threads(os.cpu_count() or 1)
     k = args.pairs if args.pairs != PAIRS_PER_GPU else 8
     ps = synth.make_pairs(range(k), H, W, D, args.desc)
     rays, pts, p0 = oracle.prep_for_iter_proj(ps["X11"], ps["X21"], None)
