@@ -147,7 +147,9 @@ constexpr int kMaxTiledRadius = 3;                   // 32 + 2*3 <= 40, 16 + 2*3
 template <int D4>
 struct TiledCfg {
     static constexpr int pitch4 = D4 + 1;                               // float4 per pixel (+16 B pad)
-    static constexpr size_t smem_bytes = (size_t)kWinX * kWinY * pitch4 * 16;
+    // + one padded row: lanes walk the warp-wide column count from their own base without a clamp,
+    // so reads may run past the end of the last window row (values discarded by the column mask)
+    static constexpr size_t smem_bytes = (size_t)(kWinX * kWinY + kWinX + 4) * pitch4 * 16;
 };
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
@@ -173,19 +175,20 @@ __device__ __forceinline__ void cp_async_wait_all() {
 // chunks and the score epilogue -- a software pipeline without a second register buffer.
 template <int D4>
 __device__ __forceinline__ const float4* cand_ptr(const float4* __restrict__ row, int col) {
-    return row + min(col, kWinX - 1) * TiledCfg<D4>::pitch4;
+    return row + col * TiledCfg<D4>::pitch4;
 }
 
 template <unsigned KMASK>
-__device__ __forceinline__ void cand_pick(const Acc4 (&a)[kQ], int pos, int i, const bool (&rowok)[kQ],
-                                          const int (&xlo)[kQ], const unsigned (&xspan)[kQ],
-                                          float (&best)[kQ], int (&bpos)[kQ]) {
+__device__ __forceinline__ void cand_pick(const Acc4 (&a)[kQ], int pos, unsigned bit,
+                                          const unsigned (&rmask)[kQ], float (&best)[kQ],
+                                          int (&bpos)[kQ]) {
 #pragma unroll
     for (int k = 0; k < kQ; ++k) {
         if ((KMASK >> k) & 1u) {
             const float sc = a[k].sum();
+            // rmask[k]: columns of this row inside query k's own window (0 when the row is not);
             // bitwise & (no short-circuit): keeps this a select, not a branch
-            const bool take = rowok[k] & ((unsigned)(i - xlo[k]) <= xspan[k]) & (sc > best[k]);
+            const bool take = ((rmask[k] & bit) != 0u) & (sc > best[k]);
             best[k] = take ? sc : best[k];
             bpos[k] = take ? pos : bpos[k];
         }
@@ -198,8 +201,7 @@ template <int D4, unsigned KMASK, bool SECOND>
 __device__ __forceinline__ void pair_eval(float4 (&c0)[D4], float4 (&c1)[D4],
                                           const float4* __restrict__ n0, const float4* __restrict__ n1,
                                           int i, int jbits, const float4 (&q)[kQ][D4],
-                                          const bool (&rowok)[kQ], const int (&xlo)[kQ],
-                                          const unsigned (&xspan)[kQ], float (&best)[kQ],
+                                          const unsigned (&rmask)[kQ], float (&best)[kQ],
                                           int (&bpos)[kQ]) {
     Acc4 a0[kQ], a1[kQ];
 #pragma unroll
@@ -214,28 +216,28 @@ __device__ __forceinline__ void pair_eval(float4 (&c0)[D4], float4 (&c1)[D4],
         c0[d] = n0[d];
         c1[d] = n1[d];
     }
-    cand_pick<KMASK>(a0, jbits | i, i, rowok, xlo, xspan, best, bpos);  // scan order: i before i+1
-    if (SECOND) cand_pick<KMASK>(a1, jbits | (i + 1), i + 1, rowok, xlo, xspan, best, bpos);
+    const unsigned bit = 1u << i;
+    cand_pick<KMASK>(a0, jbits | i, bit, rmask, best, bpos);  // scan order: i before i+1
+    if (SECOND) cand_pick<KMASK>(a1, jbits | (i + 1), bit << 1, rmask, best, bpos);
 }
 
 // `row` = this window row, `nrow` = the next one (its first pair is prefetched by the last pair here)
 template <int D4, unsigned KMASK>
 __device__ __forceinline__ void row_scan(const float4* __restrict__ row, const float4* __restrict__ nrow,
                                          int xb, int NC, int j, float4 (&c0)[D4], float4 (&c1)[D4],
-                                         const float4 (&q)[kQ][D4], const bool (&rowok)[kQ],
-                                         const int (&xlo)[kQ], const unsigned (&xspan)[kQ],
+                                         const float4 (&q)[kQ][D4], const unsigned (&rmask)[kQ],
                                          float (&best)[kQ], int (&bpos)[kQ]) {
     const int jbits = j << 16;
     int i = 0;
     for (; i + 2 < NC; i += 2)
         pair_eval<D4, KMASK, true>(c0, c1, cand_ptr<D4>(row, xb + i + 2), cand_ptr<D4>(row, xb + i + 3),
-                                   i, jbits, q, rowok, xlo, xspan, best, bpos);
+                                   i, jbits, q, rmask, best, bpos);
     const float4* __restrict__ n0 = cand_ptr<D4>(nrow, xb);
     const float4* __restrict__ n1 = cand_ptr<D4>(nrow, xb + 1);
     if (i + 1 < NC)
-        pair_eval<D4, KMASK, true>(c0, c1, n0, n1, i, jbits, q, rowok, xlo, xspan, best, bpos);
+        pair_eval<D4, KMASK, true>(c0, c1, n0, n1, i, jbits, q, rmask, best, bpos);
     else
-        pair_eval<D4, KMASK, false>(c0, c1, n0, n1, i, jbits, q, rowok, xlo, xspan, best, bpos);
+        pair_eval<D4, KMASK, false>(c0, c1, n0, n1, i, jbits, q, rmask, best, bpos);
 }
 
 template <int D4, typename PT>
@@ -361,19 +363,21 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
         xb = X0 - wx0;
         yb = Y0 - wy0;
         int nr = 0, nc = 0;
-        int ylo[kQ], xlo[kQ];
-        unsigned yspan[kQ], xspan[kQ];
+        int ylo[kQ];
+        unsigned yspan[kQ], colmask[kQ];
 #pragma unroll
         for (int k = 0; k < kQ; ++k) {
-            // candidate range of query k clipped to the image, in lane-relative coordinates;
-            // an empty range is encoded as lo = 0, span = UINT_MAX + 1 - ... -> use lo = 1<<20
+            // candidate range of query k clipped to the image, in lane-relative coordinates: rows
+            // as (lo, span) (an empty range is lo = 1 << 20), columns as a bit mask (bit i = column
+            // X0 + i).  A query whose columns do not fit 32 bits (its centre is > 25 px right of a
+            // stacked neighbour's: incoherent flow) goes to the global path.
             const int ya = max(cy[k] - radius, 0), yz = min(cy[k] + radius, H - 1);
             const int xa = max(cx[k] - radius, 0), xz = min(cx[k] + radius, W - 1);
+            if (fit[k] && xz - X0 >= 32) fit[k] = false;
             const bool any = fit[k] && ya <= yz && xa <= xz;
             ylo[k] = any ? ya - Y0 : (1 << 20);
-            xlo[k] = any ? xa - X0 : (1 << 20);
             yspan[k] = any ? (unsigned)(yz - ya) : 0u;
-            xspan[k] = any ? (unsigned)(xz - xa) : 0u;
+            colmask[k] = any ? ((0xffffffffu >> (31 - (xz - xa))) << (xa - X0)) : 0u;
             if (any) { nr = max(nr, yz - Y0 + 1); nc = max(nc, xz - X0 + 1); }
         }
         const int NR = __reduce_max_sync(0xffffffffu, nr), NC = __reduce_max_sync(0xffffffffu, nc);
@@ -386,16 +390,17 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
             for (int d = 0; d < D4; ++d) { c0[d] = p0[d]; c1[d] = p1[d]; }
         }
         for (int j = 0; j < NR; ++j) {
-            bool rowok[kQ];
+            unsigned rmask[kQ];
             unsigned kmask = 0;
 #pragma unroll
             for (int k = 0; k < kQ; ++k) {
-                rowok[k] = (unsigned)(j - ylo[k]) <= yspan[k];
-                if (__any_sync(0xffffffffu, rowok[k])) kmask |= 1u << k;
+                const bool rowok = (unsigned)(j - ylo[k]) <= yspan[k];
+                rmask[k] = rowok ? colmask[k] : 0u;
+                if (__any_sync(0xffffffffu, rowok)) kmask |= 1u << k;
             }
             const float4* __restrict__ row = tile + (min(yb + j, kWinY - 1) * kWinX) * P4;
             const float4* __restrict__ nrow = tile + (min(yb + j + 1, kWinY - 1) * kWinX) * P4;
-#define M3S_ROW(MASK) case MASK: row_scan<D4, MASK>(row, nrow, xb, NC, j, c0, c1, q, rowok, xlo, xspan, best, bpos); break
+#define M3S_ROW(MASK) case MASK: row_scan<D4, MASK>(row, nrow, xb, NC, j, c0, c1, q, rmask, best, bpos); break
             switch (kmask) {  // warp-uniform
                 case 0: {  // no query uses this row: just advance the pipeline to the next row
                     const float4* __restrict__ p0 = cand_ptr<D4>(nrow, xb);
