@@ -219,6 +219,18 @@ def main():
         "iter_proj_tile_kernel": {"ms": t_ip_ms, "alg_bytes": ALG_BYTES_ITER_PROJ * units},
         "refine_tiled_kernel": {"ms": t_rf_ms, "alg_bytes": ALG_BYTES_REFINE * units},
     }
+    # what actually bounds each kernel (ncu, profiles/): neither is HBM-bound, so the HBM fraction is
+    # reported next to the SM-pipe floor of the exact arithmetic
+    sm_ghz, sms = 1.965, 148
+    kinfo["iter_proj_tile_kernel"].update(
+        limiter="shared-memory crossbar: 288 B of fp64 corners per point-iteration (ncu: LSU wavefronts 84 % "
+                "of peak, fp64 pipe 29 %, DRAM 5 %)",
+        pipe_floor_ms=units * MAX_ITER * 69 / (62.0 * sms * sm_ghz * 1e9) * 1e3,
+        pipe_floor="69 DADD/DMUL per point-iteration at 62 fp64 lanes/clk/SM (measured)")
+    kinfo["refine_tiled_kernel"].update(
+        limiter="FMA issue at 8 warps/SM (ncu: FFMA2 = 56 % of the hot loop, FMA pipe 35 %, LSU 51 %, DRAM 17 %)",
+        pipe_floor_ms=units * 49 * 24 / (126.0 * sms * sm_ghz * 1e9) * 1e3,
+        pipe_floor="1176 FMA per pixel at 126 FMA/clk/SM (FFMA2, measured)")
     for v in kinfo.values():
         v["gbs"] = v["alg_bytes"] / (v["ms"] * 1e-3) / 1e9
     dom = max(kinfo, key=lambda k: kinfo[k]["ms"])
@@ -229,7 +241,10 @@ def main():
         "traffic": (round(load_traffic()[dom]["dram_bytes_per_px"] * units) if dom in load_traffic() else None),
         "peak_source": peak_src,
         "kernels": {k: {"ms_per_launch": round(v["ms"], 4), "alg_bytes_per_launch": v["alg_bytes"],
-                        "achieved_gbs": round(v["gbs"], 1), "frac": round(v["gbs"] / peak, 4)}
+                        "achieved_gbs": round(v["gbs"], 1), "frac": round(v["gbs"] / peak, 4),
+                        "limiter": v["limiter"], "pipe_floor_ms": round(v["pipe_floor_ms"], 4),
+                        "pipe_floor": v["pipe_floor"],
+                        "frac_of_pipe_floor": round(v["pipe_floor_ms"] / v["ms"], 4)}
                     for k, v in kinfo.items()},
         "path": {"alg_bytes_per_px": ALG_BYTES_PATH, "achieved_gbs": round(path_gbs, 1),
                  "frac": round(path_gbs / peak, 4)},

@@ -319,7 +319,7 @@ def test_full_size_config1(K, oracle, synth):
     assert np.median(err) < 0.5 and ok.mean() > 0.9
 
 
-@pytest.mark.parametrize("hw", [(50, 70), (16, 32), (37, 129)])
+@pytest.mark.parametrize("hw", [(50, 70), (16, 32), (37, 129), (16, 36)])
 def test_refine_tiled_path(K, oracle, synth, hw):
     """full-frame queries (N == H*W, D == 24): the shared-memory tiled kernel, coherent and
     incoherent centres, ragged image sizes, all radii it accepts, B = 2"""
@@ -337,7 +337,12 @@ def test_refine_tiled_path(K, oracle, synth, hw):
     sel = rng.random((b, h * w)) < 0.03
     outl[sel] = np.stack([rng.integers(-5, w + 5, sel.sum()), rng.integers(-5, h + 5, sel.sum())], -1)
     random = np.stack([rng.integers(-4, w + 4, (b, h * w)), rng.integers(-4, h + 4, (b, h * w))], -1)
-    for name, p1 in (("coherent", coherent), ("jitter", jitter), ("outliers", outl), ("random", random)):
+    # stacked queries of one thread > 25 px apart in x but all inside the 40-px staged window: their
+    # column masks do not fit 32 bits, the far ones must take the global path (same result)
+    spread = np.repeat(ident, b, 0).copy()
+    spread[..., 0] = spread[..., 0] % 4 + np.where(spread[..., 1] % 4 == 2, 28, 0)
+    for name, p1 in (("coherent", coherent), ("jitter", jitter), ("outliers", outl), ("random", random),
+                     ("spread", spread)):
         p1 = p1.astype(np.int32)
         for r in (1, 2, 3):
             out = K.refine_matches(D11, D21, p1, r, 0)
