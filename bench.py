@@ -464,8 +464,35 @@ def track_leg(dev):
             res = fn()
         e1.record()
         torch.cuda.synchronize()
-        out[name] = {"ms_per_solve": round(e0.elapsed_time(e1) / 20, 4),
+        out[name] = {"ms_per_solve_api": round(e0.elapsed_time(e1) / 20, 4),
                      "pose_err_after": float((res[0].cpu() - torch.from_numpy(d["T_WCf_gt"])).abs().max())}
+    # the same solve enqueued back to back through the C ABI on preallocated buffers (no Python
+    # tensor plumbing between launches): the device time of one cooperative launch
+    import ctypes as C
+    from mast3r_slam_b200 import _lib
+    lib = _lib.load()
+    vq, vv = Qk.reshape(-1).contiguous(), v_opt.reshape(-1).to(torch.uint8).contiguous()
+    ws = torch.empty(lib.m3s_track_workspace_bytes(NPIX), dtype=torch.uint8, device=dev)
+    o1, o2 = torch.empty(8, device=dev), torch.empty(8, device=dev)
+    stats = torch.empty(4, dtype=torch.float64, device=dev)
+    p = lambda x: C.c_void_p(x.data_ptr())  # noqa: E731
+    st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    for name, mode in (("ray_dist", _lib.TRACK_RAY_DIST), ("calib", _lib.TRACK_CALIB)):
+        prm = tracker._params(mode, tracker.get_config()["tracking"], d["K4"], (H, W))
+        call = lambda: _lib.check(lib.m3s_track_opt_pose(  # noqa: E731
+            C.byref(prm), p(Xf), p(idx), p(Xk), p(vq), p(vv), NPIX, p(Tf), p(Tk), p(o1), p(o2), p(stats),
+            p(ws), ws.numel(), st))
+        for _ in range(3):
+            call()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(50):
+            call()
+        e1.record()
+        torch.cuda.synchronize()
+        out[name]["ms_per_solve"] = round(e0.elapsed_time(e1) / 50, 4)
+        out[name]["iterations"] = int(stats.cpu()[0])
     out["points"] = NPIX
     out["valid_points"] = n_opt
     out["pose_err_before"] = float(abs(d["T_WCf"] - d["T_WCf_gt"]).max())

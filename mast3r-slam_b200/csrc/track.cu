@@ -8,18 +8,26 @@
 //                        (geometry.py:95-137), Sim3.retr = T * exp(tau) (liegroups/sim3.py:106-154,
 //                        253-262) and check_convergence (optimizer.py:11-46).
 //
-// One problem = one frame pair: N points, 7 unknowns.  Per iteration two launches and no host
-// synchronisation: `track_accum_kernel` (grid-stride over points; thread -> warp shuffle -> shared ->
-// one 36-double partial per block: 28 upper-triangular entries of J^T W J, 7 of -J^T W r, cost) and
-// `track_solve_kernel` (one CTA: fixed-order sum of the block partials, 7x7 Cholesky of H + 1e-6 I,
-// retraction, convergence test, outputs).  A device-side `done` flag turns the remaining launches
-// of the fixed-length loop into no-ops once the reference's loop would have left (`break`).
+// One problem = one frame pair: N points, 7 unknowns, ~6 MB and ~30 MFLOP per iteration: the solve is
+// latency-bound, so the WHOLE loop is ONE cooperative launch (`track_persistent_kernel`, at most
+// 2 CTAs per SM, all co-resident) with two grid-wide barriers per iteration and no host
+// synchronisation: every CTA accumulates its grid-stride share of the points (thread -> warp shuffle
+// -> shared -> one 36-double partial per CTA: 28 upper-triangular entries of J^T W J, 7 of -J^T W r,
+// cost); barrier; CTA 0 sums the partials in CTA order, factorises the 7x7 H + 1e-6 I (Cholesky),
+// retracts, tests convergence and writes the outputs; barrier; a `done` flag in global memory
+// replays the reference's `break`.
 // The reference evaluates everything in MLX fp32; here the state, the per-point arithmetic and the
 // reductions are fp64 (N is small: ~6 MB and ~30 MFLOP per iteration, the solve is latency-bound),
 // without atomics, so results are bitwise reproducible.
 #include <math.h>
 
+#include <algorithm>
+
+#include <cooperative_groups.h>
+
 #include "m3s_common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace m3s {
 
@@ -114,9 +122,9 @@ __device__ __forceinline__ void write_outputs(const TrackState* st, float* T_WCf
     }
 }
 
-__global__ void track_init_kernel(TrackState* st, const float* __restrict__ T_WCf,
-                                  const float* __restrict__ T_WCk, float* T_WCf_out,
-                                  float* T_CkCf_out, double* stats, int max_iters) {
+__device__ __forceinline__ void track_init_body(TrackState* st, const float* __restrict__ T_WCf,
+                                                const float* __restrict__ T_WCk, float* T_WCf_out,
+                                                float* T_CkCf_out, double* stats, int max_iters) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     double Tf[8], Ti[8];
     for (int k = 0; k < 8; ++k) { Tf[k] = (double)T_WCf[k]; st->Tk[k] = (double)T_WCk[k]; }
@@ -164,31 +172,53 @@ __device__ __forceinline__ void chain_row(const double* d, const double* p, doub
     J[6] = -(d[0] * p[0] + d[1] * p[1] + d[2] * p[2]);
 }
 
+// (state and partials are re-read through volatile / L2 loads: they change inside the launch)
 template <int MODE>
-__global__ void __launch_bounds__(kTrkThreads)
-track_accum_kernel(const TrackState* __restrict__ st, TrackConst c, const float* __restrict__ Xf,
-                   const int32_t* __restrict__ idx, const float* __restrict__ Xk,
-                   const float* __restrict__ Qk, const uint8_t* __restrict__ valid, int N,
-                   double* __restrict__ partial) {
-    if (st->done) return;
+__device__ __forceinline__ void
+track_accum_body(const TrackState* st, const TrackConst& c, const float* __restrict__ Xf,
+                 const int32_t* __restrict__ idx, const float* __restrict__ Xk,
+                 const float* __restrict__ Qk, const uint8_t* __restrict__ valid, int N,
+                 double* partial) {
     double T[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) T[k] = st->T[k];
+    for (int k = 0; k < 8; ++k) T[k] = reinterpret_cast<const volatile double*>(st->T)[k];
     double acc[kTrkAcc];
 #pragma unroll
     for (int k = 0; k < kTrkAcc; ++k) acc[k] = 0.0;
 
-    for (int n = blockIdx.x * kTrkThreads + threadIdx.x; n < N; n += gridDim.x * kTrkThreads) {
-        if (!__ldg(valid + n)) continue;
-        const double q = (double)__ldg(Qk + n);
-        if (!(q > 0.0)) continue;  // sqrt_info = 0: no contribution
-        const int m = idx ? __ldg(idx + n) : n;
-        if (m < 0 || m >= N) continue;
-        const double sq = sqrt(q);
-        const double X[3] = {(double)__ldg(Xf + 3 * (size_t)m), (double)__ldg(Xf + 3 * (size_t)m + 1),
-                             (double)__ldg(Xf + 3 * (size_t)m + 2)};
-        const double Y[3] = {(double)__ldg(Xk + 3 * (size_t)n), (double)__ldg(Xk + 3 * (size_t)n + 1),
-                             (double)__ldg(Xk + 3 * (size_t)n + 2)};
+    // four points per trip (same per-thread order as a plain grid-stride loop): all the index /
+    // weight loads first, then the eight gathers, then the arithmetic -- with ~5 points per thread
+    // the loop is pure load latency otherwise
+    const int stride = gridDim.x * kTrkThreads;
+    for (int n0 = blockIdx.x * kTrkThreads + threadIdx.x; n0 < N; n0 += 4 * stride) {
+      bool okp[4];
+      float qf[4];
+      int mi[4];
+      float xf[4][3], xk[4][3];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+          const int n = n0 + u * stride;
+          const bool in = n < N;
+          const int nn = in ? n : 0;
+          qf[u] = __ldg(Qk + nn);
+          mi[u] = idx ? __ldg(idx + nn) : nn;
+          okp[u] = in && (__ldg(valid + nn) != 0);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+          const int n = n0 + u * stride;
+          okp[u] = okp[u] && (qf[u] > 0.0f) && (mi[u] >= 0) && (mi[u] < N);  // sqrt_info = 0: nothing
+          const size_t m = okp[u] ? (size_t)mi[u] : 0, nn = okp[u] ? (size_t)n : 0;
+#pragma unroll
+          for (int k = 0; k < 3; ++k) { xf[u][k] = __ldg(Xf + 3 * m + k); xk[u][k] = __ldg(Xk + 3 * nn + k); }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (!okp[u]) continue;
+        const int n = n0 + u * stride;
+        const double sq = sqrt((double)qf[u]);
+        const double X[3] = {(double)xf[u][0], (double)xf[u][1], (double)xf[u][2]};
+        const double Y[3] = {(double)xk[u][0], (double)xk[u][1], (double)xk[u][2]};
         double p[3];
         quat_act(T + 3, X, p);
 #pragma unroll
@@ -236,6 +266,7 @@ track_accum_kernel(const TrackState* __restrict__ st, TrackConst c, const float*
             chain_row(d2, p, J);
             add_row(acc, J, mz - logz, si_z, c.huber);
         }
+      }
     }
     // thread -> warp (shuffle tree) -> block (fixed order over warps)
     __shared__ double sh[kTrkThreads / 32][kTrkAcc];
@@ -257,52 +288,74 @@ track_accum_kernel(const TrackState* __restrict__ st, TrackConst c, const float*
 }
 
 // One CTA.  Threads 0..35 sum the block partials in block order; thread 0 solves and updates.
-__global__ void __launch_bounds__(64)
-track_solve_kernel(TrackState* st, TrackConst c, const double* __restrict__ partial,
-                   float* T_WCf_out, float* T_CkCf_out, double* stats) {
-    if (st->done) return;
+__device__ __forceinline__ void
+track_solve_body(TrackState* st, const TrackConst& c, const double* partial, float* T_WCf_out,
+                 float* T_CkCf_out, double* stats) {
+    // fixed-order sum of the CTA partials: thread (k, part) adds CTAs part, part + 7, ...; the 7
+    // parts are then added in order (independent loads in flight instead of one serial chain)
     __shared__ double s[kTrkAcc];
+    __shared__ double sp[kTrkAcc][7];
+    if (threadIdx.x < kTrkAcc * 7) {
+        const int k = threadIdx.x / 7, part = threadIdx.x % 7;
+        double v = 0.0;
+#pragma unroll 4
+        for (int b = part; b < c.nblocks; b += 7) v += __ldcg(partial + (size_t)b * kTrkAcc + k);
+        sp[k][part] = v;
+    }
+    __syncthreads();
     if (threadIdx.x < kTrkAcc) {
         double v = 0.0;
-        for (int b = 0; b < c.nblocks; ++b) v += partial[(size_t)b * kTrkAcc + threadIdx.x];
+#pragma unroll
+        for (int part = 0; part < 7; ++part) v += sp[threadIdx.x][part];
         s[threadIdx.x] = v;
     }
     __syncthreads();
     if (threadIdx.x != 0) return;
-    // H + 1e-6 I (linalg.py:43), lower Cholesky, two triangular solves: tau = H^-1 g
-    double L[7][7], tau[7];
+    // H + 1e-6 I (linalg.py:43), lower Cholesky, two triangular solves: tau = H^-1 g.  Fully
+    // unrolled (L stays in registers, one reciprocal per pivot): this serial stretch sits between two
+    // grid barriers and was 60 % of an iteration with L in local memory.
+    double L[7][7], tau[7], rinv[7];
     {
         int k = 0;
+#pragma unroll
         for (int i = 0; i < 7; ++i)
-            for (int j = i; j < 7; ++j) { L[j][i] = s[k]; L[i][j] = s[k]; ++k; }
+#pragma unroll
+            for (int j = i; j < 7; ++j) { L[j][i] = s[k]; ++k; }
     }
     bool ok = true;
-    for (int i = 0; i < 7; ++i) L[i][i] += 1e-6;
-    for (int j = 0; j < 7 && ok; ++j) {
-        double d = L[j][j];
+#pragma unroll
+    for (int j = 0; j < 7; ++j) {
+        double d = L[j][j] + 1e-6;
+#pragma unroll
         for (int k = 0; k < j; ++k) d -= L[j][k] * L[j][k];
-        if (!(d > 0.0) || !isfinite(d)) { ok = false; break; }
+        ok = ok && (d > 0.0) && isfinite(d);
         d = sqrt(d);
         L[j][j] = d;
+        rinv[j] = 1.0 / d;
+#pragma unroll
         for (int i = j + 1; i < 7; ++i) {
             double v = L[i][j];
+#pragma unroll
             for (int k = 0; k < j; ++k) v -= L[i][k] * L[j][k];
-            L[i][j] = v / d;
+            L[i][j] = v * rinv[j];
         }
     }
-    if (ok) {
-        for (int i = 0; i < 7; ++i) {
-            double v = s[28 + i];
-            for (int k = 0; k < i; ++k) v -= L[i][k] * tau[k];
-            tau[i] = v / L[i][i];
-        }
-        for (int i = 6; i >= 0; --i) {
-            double v = tau[i];
-            for (int k = i + 1; k < 7; ++k) v -= L[k][i] * tau[k];
-            tau[i] = v / L[i][i];
-        }
-        for (int i = 0; i < 7; ++i) ok = ok && isfinite(tau[i]);
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+        double v = s[28 + i];
+#pragma unroll
+        for (int k = 0; k < i; ++k) v -= L[i][k] * tau[k];
+        tau[i] = v * rinv[i];
     }
+#pragma unroll
+    for (int i = 6; i >= 0; --i) {
+        double v = tau[i];
+#pragma unroll
+        for (int k = i + 1; k < 7; ++k) v -= L[k][i] * tau[k];
+        tau[i] = v * rinv[i];
+    }
+#pragma unroll
+    for (int i = 0; i < 7; ++i) ok = ok && isfinite(tau[i]);
     if (!ok) {  // reference: exception -> "Optimization failed", pose left as it was (tracker.py:140-142)
         st->failed = 1;
         st->done = 1;
@@ -327,6 +380,26 @@ track_solve_kernel(TrackState* st, TrackConst c, const double* __restrict__ part
     if (conv || st->iters >= c.max_iters) st->done = 1;
     write_outputs(st, T_WCf_out, T_CkCf_out);
     if (stats) { stats[0] = (double)st->iters; stats[1] = cost; stats[2] = dn; stats[3] = 0.0; }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kTrkThreads)
+track_persistent_kernel(TrackState* st, TrackConst c, const float* __restrict__ Xf,
+                        const int32_t* __restrict__ idx, const float* __restrict__ Xk,
+                        const float* __restrict__ Qk, const uint8_t* __restrict__ valid, int N,
+                        double* partial, const float* __restrict__ T_WCf,
+                        const float* __restrict__ T_WCk, float* T_WCf_out, float* T_CkCf_out,
+                        double* stats) {
+    cg::grid_group grid = cg::this_grid();
+    track_init_body(st, T_WCf, T_WCk, T_WCf_out, T_CkCf_out, stats, c.max_iters);
+    grid.sync();
+    for (int it = 0; it < c.max_iters; ++it) {
+        if (*reinterpret_cast<volatile int*>(&st->done)) break;  // same value in every CTA
+        track_accum_body<MODE>(st, c, Xf, idx, Xk, Qk, valid, N, partial);
+        grid.sync();
+        if (blockIdx.x == 0) track_solve_body(st, c, partial, T_WCf_out, T_CkCf_out, stats);
+        grid.sync();
+    }
 }
 
 // tracker.py:86-113: combined match confidence and the two validity masks, with their counts.
@@ -426,15 +499,17 @@ M3S_API int m3s_track_opt_pose(const m3s_track_params* prm, const float* Xf, con
     c.huber = prm->huber; c.rel_error = prm->rel_error; c.delta_norm = prm->delta_norm;
     c.depth_eps = prm->depth_eps;
     c.fx = prm->K4[0]; c.fy = prm->K4[1]; c.cx = prm->K4[2]; c.cy = prm->K4[3];
-    track_init_kernel<<<1, 32, 0, sst>>>(st, T_WCf, T_WCk, T_WCf_out, T_CkCf_out, stats_out, prm->max_iters);
-    for (int it = 0; it < prm->max_iters; ++it) {
-        if (rd)
-            track_accum_kernel<M3S_TRACK_RAY_DIST><<<c.nblocks, kTrkThreads, 0, sst>>>(
-                st, c, Xf, idx_f2k, Xk, Qk, valid, N, partial);
-        else
-            track_accum_kernel<M3S_TRACK_CALIB><<<c.nblocks, kTrkThreads, 0, sst>>>(
-                st, c, Xf, idx_f2k, Xk, Qk, valid, N, partial);
-        track_solve_kernel<<<1, 64, 0, sst>>>(st, c, partial, T_WCf_out, T_CkCf_out, stats_out);
-    }
+    // one cooperative launch: every CTA must be resident (<= 2 per SM by construction; clamp to what
+    // the occupancy calculator allows for this kernel)
+    const void* fn = rd ? (const void*)track_persistent_kernel<M3S_TRACK_RAY_DIST>
+                        : (const void*)track_persistent_kernel<M3S_TRACK_CALIB>;
+    int per_sm = 0;
+    M3S_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kTrkThreads, 0));
+    M3S_REQUIRE(per_sm >= 1, "track_opt_pose: kernel does not fit an SM");
+    c.nblocks = std::min(c.nblocks, per_sm * sm_count_current());
+    void* args[] = {(void*)&st, (void*)&c, (void*)&Xf, (void*)&idx_f2k, (void*)&Xk, (void*)&Qk,
+                    (void*)&valid, (void*)&N, (void*)&partial, (void*)&T_WCf, (void*)&T_WCk,
+                    (void*)&T_WCf_out, (void*)&T_CkCf_out, (void*)&stats_out};
+    M3S_CUDA(cudaLaunchCooperativeKernel(fn, dim3(c.nblocks), dim3(kTrkThreads), args, 0, sst));
     return launch_ok("track_opt_pose");
 }
