@@ -90,7 +90,7 @@ def test_iter_proj_edge_cases(K, oracle, synth):
     assert np.array_equal(pt.cpu().numpy(), po) and np.array_equal(vt.cpu().numpy(), vo)
 
 
-@pytest.mark.parametrize("impl", ["quad", "tile", "generic"])
+@pytest.mark.parametrize("impl", ["quad", "tile", "cache", "generic"])
 @pytest.mark.parametrize("hw", [(48, 64), (37, 52), (16, 36), (50, 70)])
 def test_iter_proj_full_frame_impls(K, oracle, synth, monkeypatch, impl, hw):
     """Full-frame queries (N == H*W) through each implementation (2x2-points-per-thread quad kernel
@@ -144,7 +144,7 @@ def test_iter_proj_global_break_full_frame(K, oracle, synth, monkeypatch):
     p0 = p0 + np.random.default_rng(0).uniform(-0.4, 0.4, p0.shape).astype(np.float32)
     ref = [oracle.iter_proj(rays, pts, p0, k, 1e-8, 0.0)[0] for k in range(0, 9)]
     step = [float(np.sqrt(((ref[k + 1] - ref[k]).astype(np.float32) ** 2).sum(-1)).max()) for k in range(8)]
-    for impl in ("quad", "tile", "generic"):
+    for impl in ("quad", "tile", "cache", "generic"):
         monkeypatch.setenv("M3S_ITER_PROJ_IMPL", impl)
         for k in (2, 5):
             thr = 0.5 * (step[k] + step[k - 1]) if step[k] < step[k - 1] else step[k] * 1.01
