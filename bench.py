@@ -422,10 +422,14 @@ def gn_leg(args, rank, world, dev, peak, precision):
     _lib.check(lib.m3s_gn_get_poses(sg.plan.handle, p(out), st))
     torch.cuda.synchronize()
     err0 = float(abs(g["Twc"] - g["Twc_gt"]).max())
+    exchange = sg.exchange
+    sg.close()
     return {
         "metric": "gn_iters_per_s (gauss_newton_points, 200 KF / 1000 directed edges, 196608 pts/KF)",
         "value": 1e3 / ms, "unit": "iter/s", "ms_per_iter": round(ms, 4), "iters_timed": args.gn_iters,
-        "n_gpus": world, "scaling": "strong (edges sharded, 1 all-reduce of packed H,g per iteration)",
+        "n_gpus": world, "scaling": "strong (edges sharded; packed H,g blocks exchanged once per iteration)",
+        "exchange": {"p2p": "peer stores from gn_edge_finalize_kernel over NVLink (CUDA IPC) + epoch flags",
+                     "nccl": "NCCL all-reduce of the packed blocks", "none": "single GPU"}[exchange],
         "edges_this_rank": ne, "dim": sg.plan.dim,
         "accumulate_ms": round(acc_ms, 4), "solve_update_ms": round(ms - acc_ms, 4),
         "precision": precision, "_poses": poses_after.double().cpu(),

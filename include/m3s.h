@@ -219,6 +219,26 @@ int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* params, const floa
                       const float* Cs, const int32_t* idx, const uint8_t* valid, const float* Q,
                       int edge_begin, int edge_end, m3s_stream_t stream);
 
+/* Peer exchange for edge-sharded multi-GPU solves (replaces the NCCL all-reduce of
+ * the packed blocks, which the reference has no counterpart for -- it is single-device).
+ * Once attached, m3s_gn_accumulate stores every owned edge block straight into the receive buffer
+ * of EVERY rank through NVLink peer mappings (CUDA IPC) from inside gn_edge_finalize_kernel, the
+ * last CTA publishes an epoch flag to all peers (st.release.sys), and a wait kernel on each rank
+ * acquires all flags and copies the (epoch-parity double-buffered) receive buffer into the plan's
+ * block buffer -- all enqueued on `stream`, no host synchronisation, no collective library call.
+ * Every rank must issue the same sequence of m3s_gn_accumulate calls (it is a collective).
+ *   create: allocates this rank's region, writes its 64-byte cudaIpcMemHandle to ipc_handle_out;
+ *   attach: ipc_handles = world x 64 bytes, rank-ordered (exchanged by the host, e.g.
+ *           torch.distributed.all_gather); opens the peers' regions.  The caller must barrier
+ *           after attach and before the first accumulate, and before detach / plan destroy.
+ *   detach: unmaps the peers (the rank's own region lives until the plan is destroyed; barrier
+ *           after detach on all ranks before destroying plans).
+ * A peer that does not publish within ~4 s marks the solve failed (m3s_gn_status) instead of
+ * hanging the device.  world <= 8. */
+int m3s_gn_exchange_create(m3s_gn_plan* plan, int rank, int world, void* ipc_handle_out);
+int m3s_gn_exchange_attach(m3s_gn_plan* plan, const void* ipc_handles);
+int m3s_gn_exchange_detach(m3s_gn_plan* plan);
+
 /* Assemble only: dense H (+ 1e-6 I, gauss_newton.py:254) and g from the per-edge blocks through
  * fixed-order lists (gauss_newton.py:222-251).  m3s_gn_solve_update calls it itself; exposed for
  * inspection and tests. */

@@ -84,6 +84,9 @@ SIGNATURES = {
     "m3s_gn_accumulate": (_i, [_vp, C.POINTER(GNParams), _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     "m3s_gn_assemble": (_i, [_vp, _vp]),
     "m3s_gn_solve_update": (_i, [_vp, C.POINTER(GNParams), _vp]),
+    "m3s_gn_exchange_create": (_i, [_vp, _i, _i, _vp]),
+    "m3s_gn_exchange_attach": (_i, [_vp, _vp]),
+    "m3s_gn_exchange_detach": (_i, [_vp]),
     "m3s_gn_status": (_i, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_double), _vp]),
     "m3s_gauss_newton": (_i, [_vp, C.POINTER(GNParams), _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
 }

@@ -37,7 +37,8 @@ struct Status {
     int failed;     // factorisation failed / non-finite
     int attempted;  // iterations attempted
     int chol_fail;  // scratch flag of the running factorisation
-    int pad[3];
+    int xch_timeout;  // peer exchange: a rank did not publish within the spin bound (=> failed)
+    int pad[2];
     double last_norm;
 };
 
@@ -612,20 +613,50 @@ __device__ __forceinline__ int tri_index(int r, int c) {  // r <= c, 7x7 upper
     return r * 7 - (r * (r - 1)) / 2 + (c - r);
 }
 
+// Peer exchange (multi-GPU, edge-sharded): instead of writing its block into the local buffer and
+// leaving the other ranks' slots to an NCCL all-reduce, the CTA of an OWNED edge stores the block
+// straight into the receive buffer of every rank (its own included) through NVLink peer mappings
+// (CUDA IPC); the LAST CTA of the launch then publishes the epoch number to every peer's flag word
+// (threadfence.sys + ticket counter + st.release.sys).  gn_exchange_wait_kernel on the receiving
+// side spins on its flags and copies the receive buffer (double-buffered by epoch parity, so a
+// fast peer can never overwrite blocks that are still being read) into plan->edge_blocks.
+constexpr int kMaxPeers = 8;
+struct PeerTable {
+    double* recv[kMaxPeers];                 // this epoch's receive buffer of rank r ([E, 36] f64)
+    unsigned long long* flags[kMaxPeers];    // rank r's flag words [kMaxPeers]
+    unsigned int* ticket;                    // local CTA counter
+    unsigned long long epoch;
+    int rank, world;
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+template <bool kPush>
 __global__ void __launch_bounds__(64)
 gn_edge_finalize_kernel(const Status* __restrict__ status, int mode,
                         const double* __restrict__ poses, const EdgeMeta* __restrict__ meta,
                         const double* __restrict__ partials, int nchunks, int edge_begin,
-                        int edge_end, double* __restrict__ edge_blocks) {
+                        int edge_end, double* __restrict__ edge_blocks, const PeerTable peers) {
     if (status->stopped | status->failed) return;
-    const int e = blockIdx.x;
+    // kPush: the grid covers only the owned edges
+    const int e = kPush ? edge_begin + (int)blockIdx.x : (int)blockIdx.x;
     const int tid = threadIdx.x;
-    double* out = edge_blocks + (size_t)e * kEdgeStride;
+    __shared__ double outb[kEdgeStride];
+    double* out = kPush ? outb : edge_blocks + (size_t)e * kEdgeStride;
     const EdgeMeta em = meta[e];
-    if (e < edge_begin || e >= edge_end || !em.active) {
+    const bool skip = (e < edge_begin || e >= edge_end || !em.active);
+    if (skip) {
         if (tid < kEdgeStride) out[tid] = 0.0;
-        return;
+        if (!kPush) return;
     }
+    if (!skip) {
     __shared__ double acc[kEdgeStride];
     __shared__ double S[7][7], v[7], G[7][7], T[7][7];
     const int NA = (mode == M3S_GN_CALIB) ? 35 : 29;
@@ -693,6 +724,58 @@ gn_edge_finalize_kernel(const Status* __restrict__ status, int mode,
     } else if (tid == 56) {
         out[35] = 0.0;
     }
+    }  // !skip
+    if constexpr (kPush) {
+        __shared__ unsigned int s_ticket;
+        __syncthreads();
+        if (tid < kEdgeStride) {
+            const double val = outb[tid];
+            for (int r = 0; r < peers.world; ++r) peers.recv[r][(size_t)e * kEdgeStride + tid] = val;
+            __threadfence_system();
+        }
+        __syncthreads();
+        if (tid == 0) s_ticket = atomicAdd(peers.ticket, 1u);
+        __syncthreads();
+        if (s_ticket == gridDim.x - 1) {  // every CTA's stores are fenced and counted: publish
+            __threadfence_system();
+            if (tid == 0) *peers.ticket = 0u;
+            if (tid < peers.world) st_release_sys(peers.flags[tid] + peers.rank, peers.epoch);
+        }
+    }
+}
+
+// Wait until every rank has published `epoch`, then copy the receive buffer into the plan's block
+// buffer.  A rank that owns no edges publishes from here (its finalize grid is empty).  Bounded
+// spin: a dead peer turns into status->failed after ~4 s instead of a hung GPU.
+__global__ void __launch_bounds__(256)
+gn_exchange_wait_kernel(Status* __restrict__ status, const unsigned long long* __restrict__ my_flags,
+                        const double* __restrict__ recv, double* __restrict__ edge_blocks,
+                        long long count, const PeerTable peers, int publish_here) {
+    if (status->stopped | status->failed) return;
+    __shared__ int s_ok;
+    const int tid = threadIdx.x;
+    if (tid == 0) s_ok = 1;
+    __syncthreads();
+    if (publish_here && blockIdx.x == 0 && tid < peers.world)
+        st_release_sys(peers.flags[tid] + peers.rank, peers.epoch);
+    if (tid < peers.world) {
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while (ld_acquire_sys(my_flags + tid) < peers.epoch) {
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > 4000000000ull) { s_ok = 0; break; }
+            __nanosleep(100);
+        }
+    }
+    __syncthreads();
+    if (!s_ok) {
+        if (tid == 0) { atomicExch(&status->xch_timeout, 1); atomicExch(&status->failed, 1); }
+        return;
+    }
+    for (long long i = (long long)blockIdx.x * blockDim.x + tid; i < count;
+         i += (long long)gridDim.x * blockDim.x)
+        edge_blocks[i] = recv[i];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1333,10 +1416,40 @@ struct m3s_gn_plan {
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t graph_exec = nullptr;
     bool graph_failed = false;
+    // peer exchange (m3s_gn_exchange_*): one IPC-exported allocation per rank
+    //   [2][E,36] f64 receive buffers | kMaxPeers u64 flags | u32 ticket
+    int xch_rank = 0, xch_world = 0;          // world > 1 once attached
+    bool xch_attached = false;
+    char* xch_local = nullptr;
+    char* xch_peer[kMaxPeers] = {};            // peer mappings of the same region (own = local)
+    unsigned long long xch_epoch = 0;
 };
+
+static size_t xch_recv_bytes(const m3s_gn_plan* p) {
+    return sizeof(double) * kEdgeStride * (size_t)std::max(p->E, 1);
+}
+static size_t xch_total_bytes(const m3s_gn_plan* p) {
+    return 2 * xch_recv_bytes(p) + sizeof(unsigned long long) * kMaxPeers + 64;
+}
+static void xch_unmap(m3s_gn_plan* p) {  // close the peer mappings, keep the local region
+    for (int r = 0; r < kMaxPeers; ++r) {
+        if (p->xch_peer[r] && p->xch_peer[r] != p->xch_local) cudaIpcCloseMemHandle(p->xch_peer[r]);
+        p->xch_peer[r] = nullptr;
+    }
+    p->xch_attached = false;
+    cudaGetLastError();
+}
+static void xch_free(m3s_gn_plan* p) {
+    xch_unmap(p);
+    if (p->xch_local) cudaFree(p->xch_local);
+    p->xch_local = nullptr;
+    p->xch_world = 0;
+    cudaGetLastError();
+}
 
 static void plan_free(m3s_gn_plan* p) {
     if (!p) return;
+    xch_free(p);
     if (p->graph_exec) cudaGraphExecDestroy(p->graph_exec);
     if (p->graph) cudaGraphDestroy(p->graph);
     cudaFree(p->Lm); cudaFree(p->xsol); cudaFree(p->flags); cudaFree(p->timeline);
@@ -1606,10 +1719,86 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
 #undef M3S_ACC
         if (int rc = launch_ok("gn_accum_kernel")) return rc;
     }
-    gn_edge_finalize_kernel<<<plan->E, 64, 0, st>>>(plan->status, gp->mode, plan->poses, plan->meta,
-                                                    plan->partials, (plan->N > 0) ? plan->nchunks : 0,
-                                                    edge_begin, edge_end, plan->edge_blocks);
-    return launch_ok("gn_edge_finalize_kernel");
+    PeerTable pt{};
+    if (!plan->xch_attached) {
+        gn_edge_finalize_kernel<false><<<plan->E, 64, 0, st>>>(
+            plan->status, gp->mode, plan->poses, plan->meta, plan->partials,
+            (plan->N > 0) ? plan->nchunks : 0, edge_begin, edge_end, plan->edge_blocks, pt);
+        return launch_ok("gn_edge_finalize_kernel");
+    }
+    // peer exchange: push the owned blocks to every rank, then wait for everybody's
+    const unsigned long long epoch = ++plan->xch_epoch;
+    const size_t rb = xch_recv_bytes(plan);
+    for (int r = 0; r < plan->xch_world; ++r) {
+        pt.recv[r] = reinterpret_cast<double*>(plan->xch_peer[r] + (epoch & 1) * rb);
+        pt.flags[r] = reinterpret_cast<unsigned long long*>(plan->xch_peer[r] + 2 * rb);
+    }
+    pt.ticket = reinterpret_cast<unsigned int*>(plan->xch_local + 2 * rb + sizeof(unsigned long long) * kMaxPeers);
+    pt.epoch = epoch;
+    pt.rank = plan->xch_rank;
+    pt.world = plan->xch_world;
+    if (ne > 0) {
+        gn_edge_finalize_kernel<true><<<ne, 64, 0, st>>>(
+            plan->status, gp->mode, plan->poses, plan->meta, plan->partials,
+            (plan->N > 0) ? plan->nchunks : 0, edge_begin, edge_end, plan->edge_blocks, pt);
+        if (int rc = launch_ok("gn_edge_finalize_kernel")) return rc;
+    }
+    const long long count = (long long)kEdgeStride * plan->E;
+    const int wgrid = (int)std::min<long long>((count + 255) / 256, 64);
+    gn_exchange_wait_kernel<<<wgrid, 256, 0, st>>>(
+        plan->status, reinterpret_cast<const unsigned long long*>(plan->xch_local + 2 * rb),
+        reinterpret_cast<const double*>(plan->xch_local + (epoch & 1) * rb), plan->edge_blocks, count,
+        pt, ne == 0 ? 1 : 0);
+    return launch_ok("gn_exchange_wait_kernel");
+}
+
+// ---- peer exchange setup (CUDA IPC; host plumbing exchanges the 64-byte handles) ---------------
+M3S_API int m3s_gn_exchange_create(m3s_gn_plan* plan, int rank, int world, void* ipc_handle_out) {
+    M3S_REQUIRE(plan && ipc_handle_out, "gn_exchange_create: null pointer");
+    M3S_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "gn_exchange_create: bad rank/world");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    xch_free(plan);
+    M3S_CUDA(cudaSetDevice(plan->device));
+    M3S_CUDA(cudaMalloc(reinterpret_cast<void**>(&plan->xch_local), xch_total_bytes(plan)));
+    M3S_CUDA(cudaMemset(plan->xch_local, 0, xch_total_bytes(plan)));
+    cudaIpcMemHandle_t h;
+    M3S_CUDA(cudaIpcGetMemHandle(&h, plan->xch_local));
+    memcpy(ipc_handle_out, &h, sizeof(h));
+    plan->xch_rank = rank;
+    plan->xch_world = world;
+    plan->xch_epoch = 0;
+    return M3S_OK;
+}
+
+M3S_API int m3s_gn_exchange_attach(m3s_gn_plan* plan, const void* ipc_handles) {
+    M3S_REQUIRE(plan && ipc_handles, "gn_exchange_attach: null pointer");
+    M3S_REQUIRE(plan->xch_local && plan->xch_world >= 1, "gn_exchange_attach: call m3s_gn_exchange_create first");
+    M3S_CUDA(cudaSetDevice(plan->device));
+    for (int r = 0; r < plan->xch_world; ++r) {
+        if (r == plan->xch_rank) { plan->xch_peer[r] = plan->xch_local; continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, static_cast<const char*>(ipc_handles) + (size_t)r * sizeof(h), sizeof(h));
+        void* ptr = nullptr;
+        const cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            set_error("gn_exchange_attach: cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(e));
+            for (int q = 0; q < r; ++q)
+                if (q != plan->xch_rank && plan->xch_peer[q]) { cudaIpcCloseMemHandle(plan->xch_peer[q]); plan->xch_peer[q] = nullptr; }
+            return M3S_ERR_CUDA;
+        }
+        plan->xch_peer[r] = static_cast<char*>(ptr);
+    }
+    plan->xch_attached = plan->xch_world > 1;
+    return M3S_OK;
+}
+
+M3S_API int m3s_gn_exchange_detach(m3s_gn_plan* plan) {
+    M3S_REQUIRE(plan, "gn_exchange_detach: null plan");
+    M3S_CUDA(cudaSetDevice(plan->device));
+    M3S_CUDA(cudaDeviceSynchronize());
+    xch_unmap(plan);  // the local region stays allocated until the plan dies: peers may still map it
+    return M3S_OK;
 }
 
 M3S_API int m3s_gn_assemble(m3s_gn_plan* plan, m3s_stream_t stream) {

@@ -4,11 +4,17 @@ Two shardings, nothing else:
   * matching  -- frame pairs are independent: the batch dimension is split contiguously over ranks,
                  NO collective on the data path.
   * Gauss-Newton -- directed-edge rows are split contiguously over ranks; Xs / Cs / poses are
-                 replicated.  Each iteration every rank reduces its own edges into the packed
-                 per-edge blocks buffer ([E, 36] fp64, zeros in the slots it does not own), ONE
-                 all-reduce(sum) over NCCL/NVLink fills in the others (x + 0 is exact, so the result
-                 is bit-identical to the single-GPU buffer), then every rank assembles H, g, solves
-                 and retracts redundantly -- identical inputs, identical poses, no broadcast.
+                 replicated.  Each iteration every rank reduces its own edges into packed per-edge
+                 blocks ([E, 36] fp64) and the ranks exchange them:
+                   exchange="p2p"  (default on CUDA) -- gn_edge_finalize_kernel stores each owned
+                     block directly into every rank's receive buffer over NVLink peer mappings
+                     (CUDA IPC handles exchanged once through torch.distributed) and publishes an
+                     epoch flag; a wait kernel acquires the flags.  No collective call per iteration.
+                   exchange="nccl" -- slots a rank does not own are zero, ONE all-reduce(sum) fills
+                     them in (x + 0 is exact).
+                 Either way the buffer is bit-identical to the single-GPU one; every rank then
+                 assembles H, g, solves and retracts redundantly -- identical inputs, identical
+                 poses, no broadcast.
                  The buffer is the block-sparse form of the 7F x 7F Hessian and gradient:
                  E*36*8 B (288 KB for 1000 edges) instead of 15.5 MB dense.
 """
@@ -17,6 +23,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 
+import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -89,13 +96,55 @@ class ShardedGaussNewton:
     arrays (shape [edge_end - edge_begin, N]); `ii`, `jj` describe the WHOLE graph on every rank.
     """
 
-    def __init__(self, ii, jj, num_kf, num_pts, pin, device, edge_begin, edge_end, group=None):
-        self.plan = kernels.get_plan(ii, jj, num_kf, num_pts, pin, device)
+    def __init__(self, ii, jj, num_kf, num_pts, pin, device, edge_begin, edge_end, group=None,
+                 exchange: str | None = None):
+        # a private plan (not the per-graph cache of kernels.get_plan): attaching the peer exchange
+        # changes what m3s_gn_accumulate does, which single-GPU callers of a shared plan must not see
+        ii_np = np.ascontiguousarray(np.asarray(ii, dtype=np.int32).reshape(-1))
+        jj_np = np.ascontiguousarray(np.asarray(jj, dtype=np.int32).reshape(-1))
+        self.plan = kernels.GNPlan(ii_np, jj_np, num_kf, num_pts, pin, device)
         self.device = device
         self.edge_begin, self.edge_end = int(edge_begin), int(edge_end)
         self.group = group
         self.blocks = self.plan.edge_blocks()
         self._lib = _lib.load()
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if exchange is None:
+            exchange = os.environ.get("M3S_GN_EXCHANGE", "p2p")
+        if exchange not in ("p2p", "nccl"):
+            raise ValueError(f"exchange must be 'p2p' or 'nccl', got {exchange!r}")
+        self.exchange = exchange if world > 1 else "none"
+        if self.exchange == "p2p":
+            self._attach_peers(world)
+
+    def _attach_peers(self, world: int):
+        """Exchange the CUDA IPC handles of the per-rank receive regions (host plumbing, once per
+        plan) and map the peers.  Raises on every rank if any rank cannot map its peers."""
+        lib, plan = self._lib, self.plan
+        rank = dist.get_rank(self.group)
+        torch.cuda.synchronize(self.device)   # detach + re-create must not race in-flight work
+        handle = (C.c_ubyte * 64)()
+        _lib.check(lib.m3s_gn_exchange_create(plan.handle, rank, world, handle), "gn_exchange_create")
+        mine = torch.tensor(list(bytes(handle)), dtype=torch.uint8, device=self.device)
+        every = torch.empty(world * 64, dtype=torch.uint8, device=self.device)
+        dist.all_gather_into_tensor(every, mine, group=self.group)
+        buf = (C.c_ubyte * (world * 64)).from_buffer_copy(bytes(every.cpu().numpy().tobytes()))
+        rc = lib.m3s_gn_exchange_attach(plan.handle, buf)
+        ok = torch.tensor([1 if rc == 0 else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)   # doubles as the barrier
+        if int(ok.item()) != 1:
+            msg = lib.m3s_last_error().decode() if rc != 0 else "a peer rank failed to attach"
+            lib.m3s_gn_exchange_detach(plan.handle)
+            raise _lib.M3SError(f"gn peer exchange unavailable ({msg}); pass exchange='nccl'")
+
+    def close(self):
+        """Unmap the peers (collective: every rank calls it)."""
+        if self.exchange == "p2p":
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group=self.group)
+            self._lib.m3s_gn_exchange_detach(self.plan.handle)
+            dist.barrier(group=self.group)   # every peer has unmapped before any region is freed
+            self.exchange = "closed"
 
     def _local_base(self, t, row_elems, itemsize):
         """device pointer such that row `edge_begin` of the virtual full array is t[0]"""
@@ -112,7 +161,10 @@ class ShardedGaussNewton:
                 plan.handle, C.byref(params), p(Xs), p(Cs), self._local_base(idx, n, 4),
                 self._local_base(valid, n, 1), self._local_base(Q, n, 4), self.edge_begin,
                 self.edge_end, st), "gn_accumulate")
-            allreduce_edge_blocks(self.blocks, self.group)
+            if self.exchange == "nccl":
+                allreduce_edge_blocks(self.blocks, self.group)
+            elif self.exchange == "closed":
+                raise _lib.M3SError("ShardedGaussNewton used after close()")
             _lib.check(lib.m3s_gn_solve_update(plan.handle, C.byref(params), st), "gn_solve_update")
 
     def solve(self, params, Twc, Xs, Cs, idx, valid, Q):

@@ -3,7 +3,8 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
         --master-port 29511 tests/mgpu_check.py
 
-1. edge-sharded Gauss-Newton (one NCCL all-reduce of the packed (H, g) blocks per iteration) must
+1. edge-sharded Gauss-Newton (packed (H, g) blocks exchanged once per iteration, by peer stores
+   from the finalize kernel over NVLink or by one NCCL all-reduce) must
    return exactly the poses of the single-GPU solve, on every rank (bitwise), and match the oracle;
 2. pair-sharded matching must equal the un-sharded result on the rank's slice.
 """
@@ -29,12 +30,37 @@ def main():
     idx, valid, Q = t(g["idx"], torch.int32), t(g["valid"].astype(np.uint8), torch.uint8), t(g["Q"], torch.float32)
     single = kernels.gauss_newton_points(Twc, Xs, Cs, g["ii"], g["jj"], idx, valid, Q, max_iter=6)
     eb, ee = mdist.shard_edge_range(e_total, rank, world, 2)
-    sg = mdist.ShardedGaussNewton(g["ii"], g["jj"], 24, n, 1, dev, eb, ee)
     params = kernels.make_params(_lib.GN_POINTS, 6, 1, 1e-4, 0.0, 1.5, 0.01)
-    sharded = sg.solve(params, Twc, Xs, Cs, idx[eb:ee].contiguous(), valid[eb:ee].contiguous(),
-                       Q[eb:ee].contiguous())
+    timing = {}
+    for exchange in ("nccl", "p2p", "p2p"):   # p2p twice: a second plan re-creates the mappings
+        sg = mdist.ShardedGaussNewton(g["ii"], g["jj"], 24, n, 1, dev, eb, ee, exchange=exchange)
+        assert sg.exchange == exchange
+        args = (params, Twc, Xs, Cs, idx[eb:ee].contiguous(), valid[eb:ee].contiguous(),
+                Q[eb:ee].contiguous())
+        sharded = sg.solve(*args)
+        torch.cuda.synchronize()
+        assert torch.equal(single, sharded), f"rank {rank}: {exchange}-sharded GN differs from single-GPU GN"
+        st = sg.plan.status()
+        assert not st["failed"], st
+        # repeated solves on the same plan (epochs keep counting) + device time per solve
+        torch.distributed.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            again = sg.solve(*args)
+        e1.record()
+        torch.cuda.synchronize()
+        assert torch.equal(single, again)
+        timing[exchange] = mdist.max_over_ranks(e0.elapsed_time(e1) / 10, dev)
+        sg.close()
+    # a rank that owns no edges still takes part in the exchange (publishes from the wait kernel)
+    eb0, ee0 = (0, e_total) if rank == 0 else (e_total, e_total)
+    sg = mdist.ShardedGaussNewton(g["ii"], g["jj"], 24, n, 1, dev, eb0, ee0, exchange="p2p")
+    lop = sg.solve(params, Twc, Xs, Cs, idx[eb0:ee0].contiguous(), valid[eb0:ee0].contiguous(),
+                   Q[eb0:ee0].contiguous())
     torch.cuda.synchronize()
-    assert torch.equal(single, sharded), f"rank {rank}: sharded GN differs from single-GPU GN"
+    assert torch.equal(single, lop), f"rank {rank}: lopsided p2p sharding differs"
+    sg.close()
     gathered = [torch.empty_like(sharded) for _ in range(world)]
     torch.distributed.all_gather(gathered, sharded)
     assert all(torch.equal(gathered[0], x) for x in gathered), "ranks disagree"
@@ -51,7 +77,9 @@ def main():
     assert np.array_equal(idx_s, idx_f[b:e]) and np.array_equal(valid_s, valid_f[b:e])
     torch.distributed.barrier()
     if rank == 0:
-        print(f"mgpu_check ok: world={world}, sharded GN bitwise == single GPU, pairs sharded {world}x")
+        print(f"mgpu_check ok: world={world}, sharded GN (nccl and p2p exchange) bitwise == single GPU, "
+              f"pairs sharded {world}x; ms per 6-iteration solve: " +
+              ", ".join(f"{k} {v:.3f}" for k, v in timing.items()))
     torch.distributed.destroy_process_group()
 
 
