@@ -434,7 +434,7 @@ def gn_leg(args, rank, world, dev, peak, precision):
         "accumulate_ms": round(acc_ms, 4), "solve_update_ms": round(ms - acc_ms, 4),
         "precision": precision, "_poses": poses_after.double().cpu(),
         "roofline": {"bound": "hbm",
-                     "kernel": "gn_accum_mixed_kernel" if precision == "mixed" else "gn_accum_kernel",
+                     "kernel": "gn_accum_stream_kernel" if precision == "mixed" else "gn_accum_kernel",
                      "alg_bytes_per_launch": alg,
                      "achieved": round(alg / (acc_ms * 1e-3) / 1e9, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(alg / (acc_ms * 1e-3) / 1e9 / peak, 4)},

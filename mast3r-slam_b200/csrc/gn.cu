@@ -407,6 +407,74 @@ __device__ __forceinline__ void accumulate_point_f32(const KernelParams& P, cons
     }
 }
 
+// ---- two points per instruction: the same arithmetic on the packed fp32x2 pipe ------------------
+// Blackwell's FFMA2 / FMUL2 / FADD2 take a scalar register as a broadcast operand, so the edge
+// constants cost nothing extra; lane .x / .y of every float2 is point u / u+1 of the trip.  A point
+// that fails the gate is neutralised instead of branched around (coordinates -> 0, Q -> 0 => every
+// weight is exactly 0 and every product finite), which also removes the per-point divergent branch.
+// Accumulators are float2 (even / odd points), added once at the end: fixed order, reproducible.
+#ifndef M3S_ACCF_SCALAR
+#define M3S_ACCF_PACKED 1
+#endif
+__device__ __forceinline__ float2 bc2(float c) { return make_float2(c, c); }
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
+__device__ __forceinline__ float2 sub2(float2 a, float2 b) { return __fadd2_rn(a, neg2(b)); }
+
+template <int MODE>
+__device__ __forceinline__ void accumulate_pair_f32(const KernelParams& P, const EdgeConstF& ec,
+                                                    float2 X0, float2 X1, float2 X2, float2 xix,
+                                                    float2 xiy, float2 xiz, float2 qc, float2* acc) {
+    static_assert(MODE != M3S_GN_CALIB, "calib runs the fp64 pass (see m3s_gn_accumulate)");
+    const float2 x = fma2(bc2(ec.Rh[0]), X0, fma2(bc2(ec.Rh[1]), X1, fma2(bc2(ec.Rh[2]), X2, bc2(ec.th[0]))));
+    const float2 y = fma2(bc2(ec.Rh[3]), X0, fma2(bc2(ec.Rh[4]), X1, fma2(bc2(ec.Rh[5]), X2, bc2(ec.th[1]))));
+    const float2 z = fma2(bc2(ec.Rh[6]), X0, fma2(bc2(ec.Rh[7]), X1, fma2(bc2(ec.Rh[8]), X2, bc2(ec.th[2]))));
+    const float2 xl = fma2(bc2(ec.Rl[0]), X0, fma2(bc2(ec.Rl[1]), X1, fma2(bc2(ec.Rl[2]), X2, bc2(ec.tl[0]))));
+    const float2 yl = fma2(bc2(ec.Rl[3]), X0, fma2(bc2(ec.Rl[4]), X1, fma2(bc2(ec.Rl[5]), X2, bc2(ec.tl[1]))));
+    const float2 zl = fma2(bc2(ec.Rl[6]), X0, fma2(bc2(ec.Rl[7]), X1, fma2(bc2(ec.Rl[8]), X2, bc2(ec.tl[2]))));
+    const float2 e0 = add2(sub2(x, xix), xl), e1 = add2(sub2(y, xiy), yl), e2 = add2(sub2(z, xiz), zl);
+    float2 sw = mul2(bc2(P.sig_inv_f), make_float2(sqrt_approx(qc.x), sqrt_approx(qc.y)));
+    if (MODE == M3S_GN_POINTS) {
+        const float2 d2 = fma2(xix, xix, fma2(xiy, xiy, mul2(xiz, xiz)));
+        const float2 dist = add2(make_float2(sqrt_approx(d2.x), sqrt_approx(d2.y)), bc2(1e-6f));
+        sw = mul2(sw, make_float2(rcp_approx(dist.x), rcp_approx(dist.y)));
+    }
+    const float2 w2 = mul2(sw, sw);
+    const float2 hw = mul2(bc2(kHuberF), w2);
+    const float2 a0 = mul2(sw, e0), a1 = mul2(sw, e1), a2 = mul2(sw, e2);
+    const float2 h0 = mul2(hw, make_float2(rcp_approx(fabsf(a0.x)), rcp_approx(fabsf(a0.y))));
+    const float2 h1 = mul2(hw, make_float2(rcp_approx(fabsf(a1.x)), rcp_approx(fabsf(a1.y))));
+    const float2 h2 = mul2(hw, make_float2(rcp_approx(fabsf(a2.x)), rcp_approx(fabsf(a2.y))));
+    const float2 w0 = make_float2((fabsf(a0.x) < kHuberF) ? w2.x : h0.x, (fabsf(a0.y) < kHuberF) ? w2.y : h0.y);
+    const float2 w1 = make_float2((fabsf(a1.x) < kHuberF) ? w2.x : h1.x, (fabsf(a1.y) < kHuberF) ? w2.y : h1.y);
+    const float2 w2c = make_float2((fabsf(a2.x) < kHuberF) ? w2.x : h2.x, (fabsf(a2.y) < kHuberF) ? w2.y : h2.y);
+    const float2 w0y = mul2(w0, y), w0z = mul2(w0, z), w1x = mul2(w1, x), w1z = mul2(w1, z);
+    const float2 w2x = mul2(w2c, x), w2y = mul2(w2c, y);
+    const float2 w0x = mul2(w0, x), w1y = mul2(w1, y), w2z = mul2(w2c, z);
+    acc[0] = add2(acc[0], w0); acc[1] = add2(acc[1], w1); acc[2] = add2(acc[2], w2c);
+    acc[3] = add2(acc[3], w0z); acc[4] = add2(acc[4], w0y); acc[5] = add2(acc[5], w1z);
+    acc[6] = add2(acc[6], w1x); acc[7] = add2(acc[7], w2y); acc[8] = add2(acc[8], w2x);
+    acc[9] = add2(acc[9], w0x); acc[10] = add2(acc[10], w1y); acc[11] = add2(acc[11], w2z);
+    acc[12] = fma2(w1z, z, fma2(w2y, y, acc[12]));
+    acc[13] = fma2(w0z, z, fma2(w2x, x, acc[13]));
+    acc[14] = fma2(w0y, y, fma2(w1x, x, acc[14]));
+    acc[15] = fma2(w2x, y, acc[15]);
+    acc[16] = fma2(w1x, z, acc[16]);
+    acc[17] = fma2(w0y, z, acc[17]);
+    acc[18] = fma2(sub2(w2y, w1y), z, acc[18]);
+    acc[19] = fma2(sub2(w0x, w2x), z, acc[19]);
+    acc[20] = fma2(sub2(w1x, w0x), y, acc[20]);
+    acc[21] = fma2(w0x, x, fma2(w1y, y, fma2(w2z, z, acc[21])));
+    const float2 u0 = mul2(w0, e0), u1 = mul2(w1, e1), u2 = mul2(w2c, e2);
+    acc[22] = add2(acc[22], u0); acc[23] = add2(acc[23], u1); acc[24] = add2(acc[24], u2);
+    acc[25] = add2(acc[25], fma2(y, u2, neg2(mul2(z, u1))));
+    acc[26] = add2(acc[26], fma2(z, u0, neg2(mul2(x, u2))));
+    acc[27] = add2(acc[27], fma2(x, u1, neg2(mul2(y, u0))));
+    acc[28] = fma2(x, u0, fma2(y, u1, fma2(z, u2, acc[28])));
+}
+
 #ifndef M3S_ACCF_MINBLOCKS
 #define M3S_ACCF_MINBLOCKS 2
 #endif
@@ -467,9 +535,15 @@ gn_accum_mixed_kernel(const Status* __restrict__ status, KernelParams P,
                                  // cost 25 LDS per 4 points (l1tex data pipe 67 % busy, ncu s10a)
 #endif
 
+#ifdef M3S_ACCF_PACKED
+    float2 acc2[NA];   // lane .x = even points of a trip, .y = odd points
+#pragma unroll
+    for (int k = 0; k < NA; ++k) acc2[k] = make_float2(0.0f, 0.0f);
+#else
     float acc[NA];
 #pragma unroll
     for (int k = 0; k < NA; ++k) acc[k] = 0.0f;
+#endif
 
     const float* __restrict__ Xi = Xs + (size_t)em.ix * N * 3;
     const float* __restrict__ Ci = Cs + (size_t)em.ix * N;
@@ -524,12 +598,33 @@ gn_accum_mixed_kernel(const Status* __restrict__ status, KernelParams P,
                 v4 = __ldg(v4p + gn); q4 = __ldg(q4p + gn); i4 = __ldg(i4p + gn); c4 = __ldg(c4p + gn);
                 xa = __ldg(x4p + 3 * gn); xb = __ldg(x4p + 3 * gn + 1); xc = __ldg(x4p + 3 * gn + 2);
             }
+#ifdef M3S_ACCF_PACKED
+            bool okf[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) okf[u] = okp[u] && (ci[u] > P.c_th);
+#pragma unroll
+            for (int u = 0; u < 4; u += 2) {
+                if (okf[u] | okf[u + 1]) {
+                    const bool a = okf[u], b = okf[u + 1];
+                    accumulate_pair_f32<MODE>(
+                        P, ec,
+                        make_float2(a ? xj[u][0] : 0.f, b ? xj[u + 1][0] : 0.f),
+                        make_float2(a ? xj[u][1] : 0.f, b ? xj[u + 1][1] : 0.f),
+                        make_float2(a ? xj[u][2] : 0.f, b ? xj[u + 1][2] : 0.f),
+                        make_float2(a ? xi[u][0] : 0.f, b ? xi[u + 1][0] : 0.f),
+                        make_float2(a ? xi[u][1] : 0.f, b ? xi[u + 1][1] : 0.f),
+                        make_float2(a ? xi[u][2] : 0.f, b ? xi[u + 1][2] : 0.f),
+                        make_float2(a ? qq[u] : 0.f, b ? qq[u + 1] : 0.f), acc2);
+                }
+            }
+#else
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 if (okp[u] && (ci[u] > P.c_th))
                     accumulate_point_f32<MODE>(P, ec, xj[u][0], xj[u][1], xj[u][2], xi[u][0], xi[u][1],
                                                xi[u][2], qq[u], acc);
             }
+#endif
         }
 #else
 #ifndef M3S_ACCF_UNROLL
@@ -576,16 +671,28 @@ gn_accum_mixed_kernel(const Status* __restrict__ status, KernelParams P,
             if (m < 0) m += N;
             if (m < 0 || m >= N) continue;
             if (!(qc > P.q_th) || !(__ldg(Cj + n) > P.c_th) || !(__ldg(Ci + m) > P.c_th)) continue;
+#ifdef M3S_ACCF_PACKED   // one point in lane .x, a neutral point (Q = 0 => all weights 0) in lane .y
+            accumulate_pair_f32<MODE>(P, ec, make_float2(__ldg(Xj + 3 * n), 0.f), make_float2(__ldg(Xj + 3 * n + 1), 0.f),
+                                      make_float2(__ldg(Xj + 3 * n + 2), 0.f), make_float2(__ldg(Xi + 3 * m), 0.f),
+                                      make_float2(__ldg(Xi + 3 * m + 1), 0.f), make_float2(__ldg(Xi + 3 * m + 2), 0.f),
+                                      make_float2(qc, 0.f), acc2);
+#else
             accumulate_point_f32<MODE>(P, ec, __ldg(Xj + 3 * n), __ldg(Xj + 3 * n + 1), __ldg(Xj + 3 * n + 2),
                                        __ldg(Xi + 3 * m), __ldg(Xi + 3 * m + 1), __ldg(Xi + 3 * m + 2),
                                        qc, acc);
+#endif
         }
     }
     // block reduction in fp64 through one transposed shared-memory pass: thread (k, part) sums 32
     // of the 256 per-thread partials of accumulator k (rotated start: conflict-free), the 8 parts
     // are combined by a 3-step shuffle.  Fixed order => bitwise reproducible.
+#ifdef M3S_ACCF_PACKED
+#pragma unroll
+    for (int k = 0; k < NA; ++k) red[k][threadIdx.x] = acc2[k].x + acc2[k].y;
+#else
 #pragma unroll
     for (int k = 0; k < NA; ++k) red[k][threadIdx.x] = acc[k];
+#endif
     __syncthreads();
     const int lane = threadIdx.x & 31;
     constexpr int PASSES = (NA * 8 + kAccThreads - 1) / kAccThreads;
@@ -600,6 +707,274 @@ gn_accum_mixed_kernel(const Status* __restrict__ status, KernelParams P,
         s += __shfl_down_sync(0xffffffffu, s, 2);
         s += __shfl_down_sync(0xffffffffu, s, 1);
         if (part == 0 && (id >> 3) < NA) out[id >> 3] = s;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3 (streamed): the mixed-precision pass with the five per-point streams (Xj 12 B, Q 4 B, idx 4 B,
+// Cj 4 B, valid 1 B = 25 B per point) moved by the bulk-copy engine (cp.async.bulk, 1-D TMA) into
+// a kStages-deep shared-memory ring, completion tracked by one mbarrier per stage.  ncu on the
+// register-pipelined kernel above: 36 % of the stall samples are long-scoreboard waits on the
+// FIRST use of the streamed registers -- one trip of lookahead does not cover the DRAM latency and
+// deeper lookahead costs 25 registers per trip.  Here the lookahead is (kStages - 1) trips, costs
+// no registers, and the freed registers hold the NEXT trip's (Ci, Xi) gathers while the current
+// trip is being computed (two-stage software pipeline of the idx-dependent loads).  Arithmetic is
+// accumulate_pair_f32 (packed fp32x2).  Needs N % 16 == 0, 16-B aligned arrays and chunks that are
+// multiples of the stage size; anything else takes gn_accum_mixed_kernel.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok, spins = 0;
+    do {
+        asm volatile(
+            "{\n.reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n}"
+            : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (!ok && ++spins > (1u << 24)) __trap();  // a copy that never lands must not hang the GPU
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+template <int TPB, int STAGES>
+struct StreamCfg {
+    static constexpr int kPts = TPB * 4;               // points per stage (4 per thread)
+    static constexpr int kOffX = 0;                    // Xj  [kPts * 3] f32
+    static constexpr int kOffQ = kPts * 12;            // Q   [kPts] f32
+    static constexpr int kOffI = kPts * 16;            // idx [kPts] i32
+    static constexpr int kOffC = kPts * 20;            // Cj  [kPts] f32
+    static constexpr int kOffV = kPts * 24;            // valid [kPts] u8
+    static constexpr int kStageBytes = kPts * 25;      // multiple of 16 (kPts % 16 == 0)
+    static constexpr size_t ring_bytes = (size_t)kStageBytes * STAGES;
+};
+template <int MODE, int TPB, int STAGES>
+constexpr size_t stream_smem_bytes() {
+    const size_t ring = StreamCfg<TPB, STAGES>::ring_bytes;
+    const size_t red = sizeof(float) * AccCount<MODE>::value * TPB;
+    return ring > red ? ring : red;
+}
+
+template <int MODE, int TPB, int STAGES, int MINB>
+__global__ void __launch_bounds__(TPB, MINB)
+gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
+                       const double* __restrict__ poses, const EdgeMeta* __restrict__ meta,
+                       const float* __restrict__ Xs, const float* __restrict__ Cs,
+                       const int32_t* __restrict__ idx, const uint8_t* __restrict__ valid,
+                       const float* __restrict__ Q, long long N, int edge_begin, int nchunks,
+                       long long chunk_pts, double* __restrict__ partials) {
+    if (status->stopped | status->failed) return;
+    using Cfg = StreamCfg<TPB, STAGES>;
+    constexpr int NA = AccCount<MODE>::value;
+    const int e = edge_begin + blockIdx.x / nchunks;
+    const int chunk = blockIdx.x % nchunks;
+    const EdgeMeta em = meta[e];
+    double* out = partials + ((size_t)e * nchunks + chunk) * kEdgeStride;
+    if (!em.active) return;
+
+    extern __shared__ __align__(128) unsigned char ring[];
+    __shared__ EdgeConstF ec_s;
+    __shared__ __align__(8) unsigned long long bars[STAGES];
+    const int tid = threadIdx.x;
+
+    const float* __restrict__ Xi = Xs + (size_t)em.ix * N * 3;
+    const float* __restrict__ Ci = Cs + (size_t)em.ix * N;
+    const float* __restrict__ Xj = Xs + (size_t)em.jx * N * 3;
+    const float* __restrict__ Cj = Cs + (size_t)em.jx * N;
+    const int32_t* __restrict__ ide = idx + (size_t)e * N;
+    const uint8_t* __restrict__ ve = valid + (size_t)e * N;
+    const float* __restrict__ Qe = Q + (size_t)e * N;
+    const long long n0 = (long long)chunk * chunk_pts;
+    const long long n1 = min(N, n0 + chunk_pts);
+    const int npts = (int)(n1 - n0);                       // multiple of 16
+    const int trips = (npts + Cfg::kPts - 1) / Cfg::kPts;
+    const uint32_t ring_s = smem_u32(ring), bars_s = smem_u32(bars);
+
+    auto issue = [&](int trip) {  // thread 0: arm the stage barrier and start its five copies
+        const int st = trip % STAGES;
+        const long long g0 = n0 + (long long)trip * Cfg::kPts;
+        const uint32_t cnt = (uint32_t)min((long long)Cfg::kPts, n1 - g0);
+        const uint32_t bar = bars_s + 8u * st, base = ring_s + (uint32_t)st * Cfg::kStageBytes;
+        mbar_expect_tx(bar, cnt * 25u);
+        bulk_g2s(base + Cfg::kOffX, Xj + 3 * g0, cnt * 12u, bar);
+        bulk_g2s(base + Cfg::kOffQ, Qe + g0, cnt * 4u, bar);
+        bulk_g2s(base + Cfg::kOffI, ide + g0, cnt * 4u, bar);
+        bulk_g2s(base + Cfg::kOffC, Cj + g0, cnt * 4u, bar);
+        bulk_g2s(base + Cfg::kOffV, ve + g0, cnt, bar);
+    };
+
+    if (tid == 0) {
+        for (int k = 0; k < STAGES; ++k) mbar_init(bars_s + 8u * k, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        for (int k = 0; k < STAGES && k < trips; ++k) issue(k);
+        // sim3_relative (sim3_ops.py:96-126) in fp64, then split (as gn_accum_mixed_kernel)
+        const double* Ti = poses + 8 * em.ix;
+        const double* Tj = poses + 8 * em.jx;
+        const double si_inv = 1.0 / Ti[7];
+        const double sij = si_inv * Tj[7];
+        const double qi_inv[4] = {-Ti[3], -Ti[4], -Ti[5], Ti[6]};
+        double qij[4], R[9], Ri[9];
+        quat_mul(qi_inv, Tj + 3, qij);
+        quat_to_mat(qij, R);
+        quat_to_mat(qi_inv, Ri);
+        const double d0 = Tj[0] - Ti[0], d1 = Tj[1] - Ti[1], d2 = Tj[2] - Ti[2];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+            const double v = R[k] * sij;
+            const float h = (float)v;
+            ec_s.Rh[k] = h;
+            ec_s.Rl[k] = (float)(v - (double)h);
+        }
+        const double t[3] = {(Ri[0] * d0 + Ri[1] * d1 + Ri[2] * d2) * si_inv,
+                             (Ri[3] * d0 + Ri[4] * d1 + Ri[5] * d2) * si_inv,
+                             (Ri[6] * d0 + Ri[7] * d1 + Ri[8] * d2) * si_inv};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float h = (float)t[k];
+            ec_s.th[k] = h;
+            ec_s.tl[k] = (float)(t[k] - (double)h);
+        }
+        ec_s.s_inv = (float)si_inv;
+    }
+    __syncthreads();
+    const EdgeConstF ec = ec_s;
+    const int Ni = (int)N;
+
+    float2 acc2[NA];
+#pragma unroll
+    for (int k = 0; k < NA; ++k) acc2[k] = make_float2(0.0f, 0.0f);
+
+    // per-trip state of one thread: its 4 points of the stage
+    struct Trip {
+        float xj[4][3];
+        float qq[4];
+        float ci[4], xi[4][3];
+        bool ok[4];
+    };
+    // wait for the stage, pull this thread's 4 points into registers, release the stage, start the
+    // (Ci, Xi) gathers.  Returns with the gathers in flight.
+    auto fetch = [&](int trip, Trip& T) {
+        const int st = trip % STAGES;
+        mbar_wait(bars_s + 8u * st, (uint32_t)((trip / STAGES) & 1));
+        const unsigned char* base = ring + (size_t)st * Cfg::kStageBytes;
+        // Lane l of warp w takes points w*128 + l + 32*u (u = 0..3) of the stage: for a fixed u the
+        // warp's 32 points are CONSECUTIVE, so with idx ~ identity + flow the (Ci, Xi) gathers of one
+        // LDG touch 1-2 / 3-4 cache lines instead of 4 / 12 when a thread owns 4 adjacent points
+        // (the L1 tag stage, one line per clock, was the limiter of the register-staged kernels).
+        // The shared-memory reads are conflict-free either way (word stride 1, or 3 for Xj).
+        const int j0 = (tid >> 5) * 128 + (tid & 31);
+        unsigned char vv[4];
+        int ii4[4];
+        float cc[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int j = j0 + 32 * u;
+            // points past the end of a partial last stage read stale ring bytes: harmless, the gate
+            // below fails on `in` and a failed point is neutralised before any arithmetic
+            const bool in = (trip * Cfg::kPts + j) < npts;
+            vv[u] = in ? base[Cfg::kOffV + j] : (unsigned char)0;
+            T.qq[u] = reinterpret_cast<const float*>(base + Cfg::kOffQ)[j];
+            ii4[u] = reinterpret_cast<const int*>(base + Cfg::kOffI)[j];
+            cc[u] = reinterpret_cast<const float*>(base + Cfg::kOffC)[j];
+            const float* xp = reinterpret_cast<const float*>(base + Cfg::kOffX) + 3 * j;
+            T.xj[u][0] = xp[0];
+            T.xj[u][1] = xp[1];
+            T.xj[u][2] = xp[2];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            int m = ii4[u];
+            m += (m < 0) ? Ni : 0;  // numpy negative indexing (gauss_newton.py:125)
+            T.ok[u] = vv[u] && ((unsigned)m < (unsigned)Ni) && (T.qq[u] > P.q_th) && (cc[u] > P.c_th);
+            m = T.ok[u] ? m : 0;
+            T.ci[u] = __ldg(Ci + m);
+            const float* __restrict__ xp = Xi + 3 * (size_t)(unsigned)m;
+            T.xi[u][0] = __ldg(xp); T.xi[u][1] = __ldg(xp + 1); T.xi[u][2] = __ldg(xp + 2);
+        }
+        // (placed after the gate, which consumes the shared-memory loads: they have landed)
+        // Stage hand-back without a CTA-wide stall: one named barrier per stage; warps 1.. only
+        // ARRIVE (non-blocking), warp 0 SYNCs and then re-arms the stage.  A warp cannot arrive twice
+        // on the same stage barrier before the refill it is waiting for has been issued.
+        if (tid >= 32) {
+            asm volatile("bar.arrive %0, %1;" ::"r"(1 + st), "n"(TPB) : "memory");
+        } else {
+            asm volatile("bar.sync %0, %1;" ::"r"(1 + st), "n"(TPB) : "memory");
+        }
+        if (tid == 0 && trip + STAGES < trips) issue(trip + STAGES);
+    };
+    auto compute = [&](const Trip& T) {
+        bool okf[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) okf[u] = T.ok[u] && (T.ci[u] > P.c_th);
+#ifdef M3S_ACCS_DUAL   // both pairs in one basic block (more ILP, 168 registers): measured 1.267 vs 1.257 ms
+        const bool any4 = okf[0] | okf[1] | okf[2] | okf[3];
+#endif
+#pragma unroll
+        for (int u = 0; u < 4; u += 2) {
+#ifdef M3S_ACCS_DUAL
+            if (any4) {
+#else
+            if (okf[u] | okf[u + 1]) {
+#endif
+                const bool a = okf[u], b = okf[u + 1];
+                accumulate_pair_f32<MODE>(
+                    P, ec,
+                    make_float2(a ? T.xj[u][0] : 0.f, b ? T.xj[u + 1][0] : 0.f),
+                    make_float2(a ? T.xj[u][1] : 0.f, b ? T.xj[u + 1][1] : 0.f),
+                    make_float2(a ? T.xj[u][2] : 0.f, b ? T.xj[u + 1][2] : 0.f),
+                    make_float2(a ? T.xi[u][0] : 0.f, b ? T.xi[u + 1][0] : 0.f),
+                    make_float2(a ? T.xi[u][1] : 0.f, b ? T.xi[u + 1][1] : 0.f),
+                    make_float2(a ? T.xi[u][2] : 0.f, b ? T.xi[u + 1][2] : 0.f),
+                    make_float2(a ? T.qq[u] : 0.f, b ? T.qq[u + 1] : 0.f), acc2);
+            }
+        }
+    };
+
+    if (trips > 0) {
+        Trip A, B;
+        fetch(0, A);
+        for (int t = 0; t < trips; t += 2) {   // A = trip t, its gathers in flight
+            const bool has1 = t + 1 < trips;   // CTA-uniform
+            if (has1) fetch(t + 1, B);
+            compute(A);
+            if (has1) {
+                if (t + 2 < trips) fetch(t + 2, A);
+                compute(B);
+            }
+        }
+    }
+
+    // block reduction in fp64 (fixed order, bitwise reproducible): the ring is free once every
+    // thread is past its last stage read; red[k][thread] aliases it
+    __syncthreads();
+    float* red = reinterpret_cast<float*>(ring);
+#pragma unroll
+    for (int k = 0; k < NA; ++k) red[k * TPB + tid] = acc2[k].x + acc2[k].y;
+    __syncthreads();
+    const int lane = tid & 31;
+    constexpr int PARTS = TPB / 32;
+    constexpr int PASSES = (NA * PARTS + TPB - 1) / TPB;
+#pragma unroll
+    for (int ps = 0; ps < PASSES; ++ps) {
+        const int id = ps * TPB + tid;
+        const int k = min(id / PARTS, NA - 1), part = id % PARTS;
+        double sres = 0.0;
+#pragma unroll 8
+        for (int i = 0; i < 32; ++i) sres += (double)red[k * TPB + part * 32 + ((i + lane) & 31)];
+#pragma unroll
+        for (int off = PARTS / 2; off > 0; off >>= 1) sres += __shfl_down_sync(0xffffffffu, sres, off);
+        if (part == 0 && (id / PARTS) < NA) out[id / PARTS] = sres;
     }
 }
 
@@ -1646,6 +2021,18 @@ M3S_API int m3s_gn_get_poses(m3s_gn_plan* plan, float* Twc_out, m3s_stream_t str
 }
 
 // M3S_GN_PREC_DEFAULT -> MIXED unless M3S_GN_PRECISION=f64 (read once)
+// accumulate kernel of the mixed pass: M3S_GN_ACC_IMPL = stream (default: bulk-copy ring,
+// gn_accum_stream_kernel) | regs (register-pipelined gn_accum_mixed_kernel).  Measured on B200,
+// config 5: stream 1.256 ms, regs 1.38 ms (packed) / 1.34 ms (-DM3S_ACCF_SCALAR); a 256-thread /
+// 2-CTA shape of the stream kernel spills at 128 registers and takes 1.82 ms.
+static int acc_impl() {
+    static const int v = [] {
+        const char* e = getenv("M3S_GN_ACC_IMPL");
+        return (e && !strcmp(e, "regs")) ? 0 : 1;
+    }();
+    return v;
+}
+
 static int resolve_precision(int requested) {
     if (requested == M3S_GN_PREC_F64 || requested == M3S_GN_PREC_MIXED) return requested;
     static const int env_default = [] {
@@ -1708,8 +2095,31 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
         // update (scripts/gn_precision_report.py), and its problems are 2-keyframe tracking solves
         // (config 4) where the pass takes microseconds either way
         if (resolve_precision(gp->precision) == M3S_GN_PREC_MIXED && gp->mode != M3S_GN_CALIB) {
-            if (gp->mode == M3S_GN_RAYS) M3S_ACCF(M3S_GN_RAYS);
+            // streamed kernel (bulk-copy ring): needs 16-point granularity everywhere
+            const uintptr_t al_all = al | reinterpret_cast<uintptr_t>(valid);
+            int impl = acc_impl();
+            const bool stream_ok = ((plan->N & 15) == 0) && ((al_all & 15) == 0) &&
+                                   plan->N < (1LL << 29) && (plan->chunk_pts % 1024) == 0;
+            if (!stream_ok) impl = 0;
+#define M3S_ACCS(MODE, TPB, ST, MINB)                                                            \
+    do {                                                                                         \
+        auto fn = gn_accum_stream_kernel<MODE, TPB, ST, MINB>;                                   \
+        constexpr size_t sm = stream_smem_bytes<MODE, TPB, ST>();                                \
+        static bool attr_done = false;                                                           \
+        if (!attr_done) {                                                                        \
+            M3S_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
+            attr_done = true;                                                                    \
+        }                                                                                        \
+        fn<<<grid, TPB, sm, st>>>(plan->status, P, plan->poses, plan->meta, Xs, Cs, idx, valid, Q, \
+                                  plan->N, edge_begin, plan->nchunks, plan->chunk_pts,           \
+                                  plan->partials);                                               \
+    } while (0)
+            if (impl == 1) {
+                if (gp->mode == M3S_GN_RAYS) M3S_ACCS(M3S_GN_RAYS, 128, 4, 3);
+                else M3S_ACCS(M3S_GN_POINTS, 128, 4, 3);
+            } else if (gp->mode == M3S_GN_RAYS) M3S_ACCF(M3S_GN_RAYS);
             else M3S_ACCF(M3S_GN_POINTS);
+#undef M3S_ACCS
         } else {
             if (gp->mode == M3S_GN_RAYS) M3S_ACC(M3S_GN_RAYS);
             else if (gp->mode == M3S_GN_POINTS) M3S_ACC(M3S_GN_POINTS);

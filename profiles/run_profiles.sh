@@ -13,7 +13,7 @@ KREGEX='regex:iter_proj|refine_|gn_|chol_|prep_kernel|match_tail'
 $CMD > $OUT/plain_$TAG.log 2>&1 || { echo "plain run failed"; tail -20 $OUT/plain_$TAG.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KREGEX" -c 1500 --csv \
     --log-file $OUT/launches_$TAG.csv $CMD > $OUT/ncu_list_$TAG.log 2>&1
-for spec in "iter_proj_tile_kernel:4" "refine_tiled_kernel:3" "gn_accum_mixed_kernel:2"; do
+for spec in "iter_proj_tile_kernel:4" "refine_tiled_kernel:3" "gn_accum_stream_kernel:2"; do
   k=${spec%%:*}; s=${spec##*:}
   ncu --set full --clock-control none --import-source on -k regex:$k -s $s -c 1 -f \
       -o $OUT/prof_${k}_$TAG $CMD > $OUT/ncu_${k}_$TAG.log 2>&1
