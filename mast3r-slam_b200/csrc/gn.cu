@@ -2105,11 +2105,8 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
     do {                                                                                         \
         auto fn = gn_accum_stream_kernel<MODE, TPB, ST, MINB>;                                   \
         constexpr size_t sm = stream_smem_bytes<MODE, TPB, ST>();                                \
-        static bool attr_done = false;                                                           \
-        if (!attr_done) {                                                                        \
-            M3S_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
-            attr_done = true;                                                                    \
-        }                                                                                        \
+        /* per device, so not cached in a static: a process may drive several devices */        \
+        M3S_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
         fn<<<grid, TPB, sm, st>>>(plan->status, P, plan->poses, plan->meta, Xs, Cs, idx, valid, Q, \
                                   plan->N, edge_begin, plan->nchunks, plan->chunk_pts,           \
                                   plan->partials);                                               \
