@@ -223,12 +223,12 @@ def main():
     # reported next to the SM-pipe floor of the exact arithmetic
     sm_ghz, sms = 1.965, 148
     kinfo["iter_proj_tile_kernel"].update(
-        limiter="shared-memory crossbar: 288 B of fp64 corners per point-iteration (ncu: LSU wavefronts 84 % "
-                "of peak, fp64 pipe 29 %, DRAM 5 %)",
+        limiter="shared-memory crossbar: 288 B of fp64 corners per point-iteration (ncu s17: LSU wavefronts "
+                "86 % of peak, issue 66 %, fp64 pipe 31 %, XU 34 %, DRAM 6 %)",
         pipe_floor_ms=units * MAX_ITER * 69 / (62.0 * sms * sm_ghz * 1e9) * 1e3,
         pipe_floor="69 DADD/DMUL per point-iteration at 62 fp64 lanes/clk/SM (measured)")
     kinfo["refine_tiled_kernel"].update(
-        limiter="FMA issue at 8 warps/SM (ncu: FFMA2 = 56 % of the hot loop, FMA pipe 35 %, LSU 51 %, DRAM 17 %)",
+        limiter="FMA issue at 8 warps/SM (ncu s17: FFMA2 = 56 % of the hot loop, FMA pipe 40 %, LSU 58 %, DRAM 19 %)",
         pipe_floor_ms=units * 49 * 24 / (126.0 * sms * sm_ghz * 1e9) * 1e3,
         pipe_floor="1176 FMA per pixel at 126 FMA/clk/SM (FFMA2, measured)")
     for v in kinfo.values():
