@@ -281,3 +281,49 @@ def test_full_size_config5_points(K, oracle, synth):
     torch.cuda.empty_cache()
     ref = oracle.gauss_newton_points(*gargs(h), max_iter=2)
     assert upd_err(out.cpu().numpy(), ref, h["Twc"]) <= REL
+
+
+@pytest.mark.parametrize("mode", ["rays", "points"])
+@pytest.mark.parametrize("npts", [592, 2000, 4112])
+def test_gn_streamed_partial_stages(K, oracle, synth, mode, npts):
+    """N % 16 == 0 but not a multiple of the 512-point ring stage: the streamed accumulate kernel
+    (cp.async.bulk ring) runs a partial last stage whose tail lanes read stale ring bytes and must
+    be gated out; 592 < one stage, 2000 = 3 stages + 464, 4112 = 8 stages + 16."""
+    g = synth.make_graph(21 + npts % 7, 6, 2, 96, 128, num_pts=npts)
+    fn = "gauss_newton_" + mode
+    out = getattr(K, fn)(*gargs(g), max_iter=6)
+    ref = getattr(oracle, fn)(*gargs(g), max_iter=6)
+    assert upd_err(out, ref, g["Twc"]) <= REL
+
+
+@pytest.mark.parametrize("mode", ["rays", "points"])
+def test_gn_gated_points_cannot_poison(K, synth, mode):
+    """The packed accumulate neutralises gated-out points instead of branching around them: NaN /
+    Inf coordinates, confidences and Q of points that fail the gate (valid = 0, Q <= Q_thresh,
+    C <= C_thresh, idx out of range) must leave the result bit-identical, as in the reference,
+    which never touches them (gauss_newton.py:129)."""
+    g = synth.make_graph(5, 6, 2, 96, 128, num_pts=2048)
+    fn = getattr(K, "gauss_newton_" + mode)
+    clean = fn(*gargs(g), max_iter=4)
+    rng = np.random.default_rng(0)
+    h = {k: np.array(v, copy=True) for k, v in g.items() if isinstance(v, np.ndarray)}
+    valid = h["valid"].reshape(len(h["ii"]), -1).copy()
+    Q = h["Q"].reshape(valid.shape).copy()
+    idx = h["idx"].reshape(valid.shape).copy()
+    # per edge: points that are invalid get garbage Q / idx; a few valid ones are gated by Q instead
+    bad = ~valid.astype(bool)
+    Q[bad] = rng.choice([np.nan, np.inf, -np.inf, 1e30], size=int(bad.sum())).astype(np.float32)
+    idx[bad] = rng.integers(-10 * 2048, 10 * 2048, size=int(bad.sum()))
+    h["Q"], h["idx"] = Q.reshape(h["Q"].shape), idx.reshape(h["idx"].shape)
+    # keyframe points that no valid match ever reads (as source or as target) become NaN / Inf
+    n = 2048
+    used = np.zeros((h["Xs"].shape[0], n), bool)
+    for e, (i, j) in enumerate(zip(h["ii"], h["jj"])):
+        v = valid[e].astype(bool)
+        used[j, v] = True
+        used[i, idx[e][v] % n] = True
+    Xs = h["Xs"].reshape(-1, n, 3)
+    Xs[~used] = np.nan
+    h["Xs"] = Xs.reshape(h["Xs"].shape)
+    out = fn(*[h[k] for k in ("Twc", "Xs", "Cs", "ii", "jj", "idx", "valid", "Q")], max_iter=4)
+    assert np.array_equal(out, clean)
