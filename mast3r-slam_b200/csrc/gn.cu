@@ -1249,6 +1249,15 @@ __device__ __forceinline__ double rsqrt_fast(double d) {
     return fma(y, e, y);
 }
 
+// 1 / d for 1e-290 < d < 1e300: hardware seed (~2^-20) + one third-order step (error e^3)
+__device__ __forceinline__ double rcp_fast(double d) {
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+    const double e = fma(-d, y, 1.0);
+    const double t = fma(e, e, e);
+    return fma(y, t, y);
+}
+
 // 32x32 Cholesky by ONE warp, row `lane` of the block in registers, no block barrier on the 32-step
 // dependent chain.  Column j:
 //   critical part (shuffles only): d_j and the entries a[j+1][j], a[j+2][j] are broadcast by three
@@ -1298,6 +1307,73 @@ __device__ __forceinline__ bool chol32_warp(double (*W)[kNB + 1], double (*L)[kN
 #pragma unroll
     for (int c = 0; c < kNB; ++c) L[lane][c] = (c <= lane) ? a[c] : 0.0;
     return !bad;
+}
+
+// 32x32 Cholesky by the whole CTA (>= 64 threads), blocked in 4 panels of 8 columns.  Warp 0
+// factorises a panel with the rows in registers (8 entries per lane); per column the dependent chain
+// is shuffle(d) -> reciprocal -> update of the <= 7 remaining panel columns, whose multipliers
+// are shuffled before the reciprocal (independent of it) -- no shared-memory traffic and no
+// bulk update on the chain.  The trailing update of the columns right of the panel (<= 300 entries
+// x 8 FMAs) is spread over all threads between two barriers.  Measured against the one-warp
+// left-looking version above (scripts/gn_solve_timeline.py, B200): diag CTA 8.84 vs 8.97 us per block
+// step, solve 0.609 vs 0.616 ms -- the 32-column chain is not what the ~5 us of a block are made of.
+constexpr int kCholPanel = 8;
+__device__ __forceinline__ bool chol32_block(double (*W)[kNB + 1], double (*L)[kNB + 1], double* dinv,
+                                             int* bad_flag) {
+    const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31;
+#pragma unroll 1
+    for (int c0 = 0; c0 < kNB; c0 += kCholPanel) {
+        if (tid < 32) {
+            double a[kCholPanel];
+#pragma unroll
+            for (int j = 0; j < kCholPanel; ++j) a[j] = W[lane][c0 + j];  // rows < c0 + j: unused garbage-free zeros
+            bool bad = false;
+            double Dj[kCholPanel];
+            // LDL^T-style inside the panel: columns stay UNSCALED (u = l * sqrt(D)) while the chain
+            // runs, so a column step is shuffle -> reciprocal (MUFU + 3 fp64 ops) -> 2 fp64 ops
+            // instead of shuffle -> rsqrt (MUFU + 6) -> 3: fp64 latency (~25 clk) is what the 32-step
+            // chain is made of.  The square roots are taken afterwards, all 8 independent.
+#pragma unroll
+            for (int j = 0; j < kCholPanel; ++j) {
+                double d = __shfl_sync(0xffffffffu, a[j], c0 + j);
+                double nv[kCholPanel];
+#pragma unroll
+                for (int c = j + 1; c < kCholPanel; ++c) nv[c] = __shfl_sync(0xffffffffu, a[j], c0 + c);
+                if (!((d > 1e-290) && (d < 1e300))) { bad = true; d = 1.0; }  // warp-uniform
+                Dj[j] = d;
+                const double t = a[j] * rcp_fast(d);
+#pragma unroll
+                for (int c = j + 1; c < kCholPanel; ++c) a[c] -= t * nv[c];
+            }
+#pragma unroll
+            for (int j = 0; j < kCholPanel; ++j) {
+                const double rs = rsqrt_fast(Dj[j]);
+                const double l = (lane == c0 + j) ? Dj[j] * rs : a[j] * rs;
+                if (lane >= c0 + j) W[lane][c0 + j] = l;
+                if (lane == c0 + j) dinv[c0 + j] = rs;
+            }
+            if (bad && lane == 0) *bad_flag = 1;
+        }
+        __syncthreads();
+        const int m0 = c0 + kCholPanel;          // first trailing row / column
+        const int m = kNB - m0;                  // trailing size
+        for (int i = tid; i < m * m; i += nt) {
+            const int r = m0 + i / m, c = m0 + i % m;
+            if (c <= r) {
+                double sacc = 0.0;
+#pragma unroll
+                for (int j = 0; j < kCholPanel; ++j) sacc += W[r][c0 + j] * W[c][c0 + j];
+                W[r][c] -= sacc;
+            }
+        }
+        __syncthreads();
+    }
+    for (int i = tid; i < kNB * kNB; i += nt) {
+        const int r = i / kNB, c = i % kNB;
+        L[r][c] = (c <= r) ? W[r][c] : 0.0;
+    }
+    __syncthreads();
+    return *bad_flag == 0;
 }
 
 // Column `lane` of the inverse of the lower-triangular 32x32 block L (shared memory), by forward
@@ -1379,10 +1455,14 @@ __device__ __forceinline__ void chol_diag_block(DiagSmem& sm, Status* __restrict
         }
     }
     __syncthreads();
+#ifdef M3S_CHOL_WARP   // the one-warp left-looking version (A/B)
     if (tid < 32) {
         if (!chol32_warp(sm.W, sm.L, sm.dinv, sm.col, tid) && tid == 0) sm.bad = 1;
     }
     __syncthreads();
+#else
+    chol32_block(sm.W, sm.L, sm.dinv, &sm.bad);
+#endif
     if (sm.bad) {
         if (tid == 0) status->chol_fail = 1;
         return;
