@@ -1510,6 +1510,11 @@ __global__ void __launch_bounds__(kStepThreads, 2)  // 2 CTAs / SM: the 255 tile
 chol_step_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* __restrict__ Lm,
                  double* __restrict__ Ldiag, double* __restrict__ Linv, int np, int kb, int ntc,
                  long long* __restrict__ tl) {
+    // Programmatic dependent launch (when the launch carries the attribute; no-ops otherwise): let
+    // the NEXT block step's CTAs be scheduled while this grid is still running, and do not touch
+    // anything the previous grid wrote before it has completed and flushed.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     if (status->stopped | status->failed | status->chol_fail) return;
     __shared__ StepSmem sm;
     const int tid = threadIdx.x;
@@ -2307,6 +2312,18 @@ M3S_API int m3s_gn_assemble(m3s_gn_plan* plan, m3s_stream_t stream) {
     return M3S_OK;
 }
 
+// M3S_GN_PDL=1 launches the block steps with programmatic stream serialisation (the kernel's
+// griddepcontrol.wait orders them).  MEASURED on B200 (config 5): solve 0.635 ms with, 0.606 ms
+// without -- the early-resident CTAs of later steps cost more than the launch gaps they hide; off by
+// default, kept for A/B.
+static bool use_pdl() {
+    static const bool v = [] {
+        const char* e = getenv("M3S_GN_PDL");
+        return e && e[0] == '1';
+    }();
+    return v;
+}
+
 // assemble + blocked Cholesky of the augmented matrix, enqueued on `st`: one launch per block step
 static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
     if (int rc = m3s_gn_assemble(plan, reinterpret_cast<m3s_stream_t>(st))) return rc;
@@ -2323,9 +2340,27 @@ static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
         const int ntc = (trailing + kSyrkTile - 1) / kSyrkTile;
         // trailing == 0 (last step): one tile that only solves the rhs row
         const int ntiles = (ntc == 0) ? 1 : ntc * (ntc + 1) / 2 + ((ntr > ntc) ? ntc : 0);
-        chol_step_kernel<<<2 + ntiles, kStepThreads, 0, st>>>(plan->status, plan->Hm, plan->Lm,
-                                                             plan->Ldiag, plan->Linv, np, kb,
-                                                             std::max(ntc, 1), plan->timeline);
+        if (use_pdl() && kb > 0) {
+            // block step kb depends on step kb - 1 only: programmatic edge (also inside the captured
+            // graph), the kernel's griddepcontrol.wait provides the ordering
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(2 + ntiles);
+            cfg.blockDim = dim3(kStepThreads);
+            cfg.dynamicSmemBytes = 0;
+            cfg.stream = st;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = at;
+            cfg.numAttrs = 1;
+            M3S_CUDA(cudaLaunchKernelEx(&cfg, chol_step_kernel, plan->status, plan->Hm, plan->Lm,
+                                        plan->Ldiag, plan->Linv, np, kb, std::max(ntc, 1),
+                                        plan->timeline));
+        } else {
+            chol_step_kernel<<<2 + ntiles, kStepThreads, 0, st>>>(plan->status, plan->Hm, plan->Lm,
+                                                                 plan->Ldiag, plan->Linv, np, kb,
+                                                                 std::max(ntc, 1), plan->timeline);
+        }
         if (int rc = launch_ok("chol_step_kernel")) return rc;
     }
     return M3S_OK;
