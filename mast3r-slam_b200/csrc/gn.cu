@@ -765,7 +765,11 @@ constexpr size_t stream_smem_bytes() {
     return ring > red ? ring : red;
 }
 
-template <int MODE, int TPB, int STAGES, int MINB>
+// kSlim: Xj and Q of a trip are NOT carried in registers while its gathers are in flight; they are
+// re-read from the ring when the trip is computed and the stage is handed back after that (one trip
+// later).  The in-flight trip then costs 17 registers instead of 33, which is what separates 3 from 4
+// resident CTAs per SM.
+template <int MODE, int TPB, int STAGES, int MINB, bool kSlim>
 __global__ void __launch_bounds__(TPB, MINB)
 gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
                        const double* __restrict__ poses, const EdgeMeta* __restrict__ meta,
@@ -785,7 +789,9 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
     extern __shared__ __align__(128) unsigned char ring[];
     __shared__ EdgeConstF ec_s;
     __shared__ __align__(8) unsigned long long bars[STAGES];
+    __shared__ unsigned int stage_cnt[STAGES];
     const int tid = threadIdx.x;
+    if (tid < STAGES) stage_cnt[tid] = 0u;
 
     const float* __restrict__ Xi = Xs + (size_t)em.ix * N * 3;
     const float* __restrict__ Ci = Cs + (size_t)em.ix * N;
@@ -857,10 +863,25 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
 
     // per-trip state of one thread: its 4 points of the stage
     struct Trip {
-        float xj[4][3];
-        float qq[4];
+        float xj[kSlim ? 1 : 4][3];   // kSlim: unused
+        float qq[kSlim ? 1 : 4];
         float ci[4], xi[4][3];
         bool ok[4];
+    };
+    auto release = [&](int trip) {
+        // Stage hand-back without anybody waiting: every warp counts itself out of the stage
+        // (shared-memory atomic, ordered behind its ring reads in the LSU queue); the LAST warp to
+        // leave re-arms the stage.  (A fixed producer warp that bar.sync'ed on the others spent half
+        // of its time in that barrier: ncu s17, 12.6 % of all stall samples.)
+        const int st = trip % STAGES;
+        __syncwarp();
+        if ((tid & 31) == 0) {
+            const unsigned int old = atomicAdd(&stage_cnt[st], 1u);
+            if (old == TPB / 32 - 1) {
+                stage_cnt[st] = 0u;
+                if (trip + STAGES < trips) issue(trip + STAGES);
+            }
+        }
     };
     // wait for the stage, pull this thread's 4 points into registers, release the stage, start the
     // (Ci, Xi) gathers.  Returns with the gathers in flight.
@@ -876,7 +897,7 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
         const int j0 = (tid >> 5) * 128 + (tid & 31);
         unsigned char vv[4];
         int ii4[4];
-        float cc[4];
+        float cc[4], qg[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int j = j0 + 32 * u;
@@ -884,39 +905,52 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
             // below fails on `in` and a failed point is neutralised before any arithmetic
             const bool in = (trip * Cfg::kPts + j) < npts;
             vv[u] = in ? base[Cfg::kOffV + j] : (unsigned char)0;
-            T.qq[u] = reinterpret_cast<const float*>(base + Cfg::kOffQ)[j];
+            qg[u] = reinterpret_cast<const float*>(base + Cfg::kOffQ)[j];
             ii4[u] = reinterpret_cast<const int*>(base + Cfg::kOffI)[j];
             cc[u] = reinterpret_cast<const float*>(base + Cfg::kOffC)[j];
-            const float* xp = reinterpret_cast<const float*>(base + Cfg::kOffX) + 3 * j;
-            T.xj[u][0] = xp[0];
-            T.xj[u][1] = xp[1];
-            T.xj[u][2] = xp[2];
+            if constexpr (!kSlim) {
+                const float* xp = reinterpret_cast<const float*>(base + Cfg::kOffX) + 3 * j;
+                T.qq[u] = qg[u];
+                T.xj[u][0] = xp[0];
+                T.xj[u][1] = xp[1];
+                T.xj[u][2] = xp[2];
+            }
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             int m = ii4[u];
             m += (m < 0) ? Ni : 0;  // numpy negative indexing (gauss_newton.py:125)
-            T.ok[u] = vv[u] && ((unsigned)m < (unsigned)Ni) && (T.qq[u] > P.q_th) && (cc[u] > P.c_th);
+            T.ok[u] = vv[u] && ((unsigned)m < (unsigned)Ni) && (qg[u] > P.q_th) && (cc[u] > P.c_th);
             m = T.ok[u] ? m : 0;
             T.ci[u] = __ldg(Ci + m);
             const float* __restrict__ xp = Xi + 3 * (size_t)(unsigned)m;
             T.xi[u][0] = __ldg(xp); T.xi[u][1] = __ldg(xp + 1); T.xi[u][2] = __ldg(xp + 2);
         }
         // (placed after the gate, which consumes the shared-memory loads: they have landed)
-        // Stage hand-back without a CTA-wide stall: one named barrier per stage; warps 1.. only
-        // ARRIVE (non-blocking), warp 0 SYNCs and then re-arms the stage.  A warp cannot arrive twice
-        // on the same stage barrier before the refill it is waiting for has been issued.
-        if (tid >= 32) {
-            asm volatile("bar.arrive %0, %1;" ::"r"(1 + st), "n"(TPB) : "memory");
-        } else {
-            asm volatile("bar.sync %0, %1;" ::"r"(1 + st), "n"(TPB) : "memory");
-        }
-        if (tid == 0 && trip + STAGES < trips) issue(trip + STAGES);
+        if constexpr (!kSlim) release(trip);
     };
-    auto compute = [&](const Trip& T) {
+    auto compute = [&](int trip, const Trip& T) {
         bool okf[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) okf[u] = T.ok[u] && (T.ci[u] > P.c_th);
+        float xj[4][3], qq[4];
+        if constexpr (kSlim) {
+            const unsigned char* base = ring + (size_t)(trip % STAGES) * Cfg::kStageBytes;
+            const int j0 = (tid >> 5) * 128 + (tid & 31);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int j = j0 + 32 * u;
+                const float* xp = reinterpret_cast<const float*>(base + Cfg::kOffX) + 3 * j;
+                qq[u] = reinterpret_cast<const float*>(base + Cfg::kOffQ)[j];
+                xj[u][0] = xp[0]; xj[u][1] = xp[1]; xj[u][2] = xp[2];
+            }
+        } else {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                qq[u] = T.qq[u];
+                xj[u][0] = T.xj[u][0]; xj[u][1] = T.xj[u][1]; xj[u][2] = T.xj[u][2];
+            }
+        }
 #ifdef M3S_ACCS_DUAL   // both pairs in one basic block (more ILP, 168 registers): measured 1.267 vs 1.257 ms
         const bool any4 = okf[0] | okf[1] | okf[2] | okf[3];
 #endif
@@ -930,15 +964,16 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
                 const bool a = okf[u], b = okf[u + 1];
                 accumulate_pair_f32<MODE>(
                     P, ec,
-                    make_float2(a ? T.xj[u][0] : 0.f, b ? T.xj[u + 1][0] : 0.f),
-                    make_float2(a ? T.xj[u][1] : 0.f, b ? T.xj[u + 1][1] : 0.f),
-                    make_float2(a ? T.xj[u][2] : 0.f, b ? T.xj[u + 1][2] : 0.f),
+                    make_float2(a ? xj[u][0] : 0.f, b ? xj[u + 1][0] : 0.f),
+                    make_float2(a ? xj[u][1] : 0.f, b ? xj[u + 1][1] : 0.f),
+                    make_float2(a ? xj[u][2] : 0.f, b ? xj[u + 1][2] : 0.f),
                     make_float2(a ? T.xi[u][0] : 0.f, b ? T.xi[u + 1][0] : 0.f),
                     make_float2(a ? T.xi[u][1] : 0.f, b ? T.xi[u + 1][1] : 0.f),
                     make_float2(a ? T.xi[u][2] : 0.f, b ? T.xi[u + 1][2] : 0.f),
-                    make_float2(a ? T.qq[u] : 0.f, b ? T.qq[u + 1] : 0.f), acc2);
+                    make_float2(a ? qq[u] : 0.f, b ? qq[u + 1] : 0.f), acc2);
             }
         }
+        if constexpr (kSlim) release(trip);   // the arithmetic above consumed the ring reads
     };
 
     if (trips > 0) {
@@ -947,10 +982,10 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
         for (int t = 0; t < trips; t += 2) {   // A = trip t, its gathers in flight
             const bool has1 = t + 1 < trips;   // CTA-uniform
             if (has1) fetch(t + 1, B);
-            compute(A);
+            compute(t, A);
             if (has1) {
                 if (t + 2 < trips) fetch(t + 2, A);
-                compute(B);
+                compute(t + 1, B);
             }
         }
     }
@@ -2113,7 +2148,9 @@ M3S_API int m3s_gn_get_poses(m3s_gn_plan* plan, float* Twc_out, m3s_stream_t str
 static int acc_impl() {
     static const int v = [] {
         const char* e = getenv("M3S_GN_ACC_IMPL");
-        return (e && !strcmp(e, "regs")) ? 0 : 1;
+        if (e && !strcmp(e, "regs")) return 0;
+        if (e && !strcmp(e, "slim")) return 2;
+        return 1;
     }();
     return v;
 }
@@ -2186,9 +2223,9 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
             const bool stream_ok = ((plan->N & 15) == 0) && ((al_all & 15) == 0) &&
                                    plan->N < (1LL << 29) && (plan->chunk_pts % 1024) == 0;
             if (!stream_ok) impl = 0;
-#define M3S_ACCS(MODE, TPB, ST, MINB)                                                            \
+#define M3S_ACCS(MODE, TPB, ST, MINB, SLIM)                                                          \
     do {                                                                                         \
-        auto fn = gn_accum_stream_kernel<MODE, TPB, ST, MINB>;                                   \
+        auto fn = gn_accum_stream_kernel<MODE, TPB, ST, MINB, SLIM>;                             \
         constexpr size_t sm = stream_smem_bytes<MODE, TPB, ST>();                                \
         /* per device, so not cached in a static: a process may drive several devices */        \
         M3S_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
@@ -2197,8 +2234,11 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
                                   plan->partials);                                               \
     } while (0)
             if (impl == 1) {
-                if (gp->mode == M3S_GN_RAYS) M3S_ACCS(M3S_GN_RAYS, 128, 4, 3);
-                else M3S_ACCS(M3S_GN_POINTS, 128, 4, 3);
+                if (gp->mode == M3S_GN_RAYS) M3S_ACCS(M3S_GN_RAYS, 128, 4, 3, false);
+                else M3S_ACCS(M3S_GN_POINTS, 128, 4, 3, false);
+            } else if (impl == 2) {
+                if (gp->mode == M3S_GN_RAYS) M3S_ACCS(M3S_GN_RAYS, 128, 4, 4, true);
+                else M3S_ACCS(M3S_GN_POINTS, 128, 4, 4, true);
             } else if (gp->mode == M3S_GN_RAYS) M3S_ACCF(M3S_GN_RAYS);
             else M3S_ACCF(M3S_GN_POINTS);
 #undef M3S_ACCS
