@@ -2234,8 +2234,8 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
                                   plan->partials);                                               \
     } while (0)
             if (impl == 1) {
-                if (gp->mode == M3S_GN_RAYS) M3S_ACCS(M3S_GN_RAYS, 128, 4, 3, false);
-                else M3S_ACCS(M3S_GN_POINTS, 128, 4, 3, false);
+                if (gp->mode == M3S_GN_RAYS) M3S_ACCS(M3S_GN_RAYS, 128, 5, 3, false);
+                else M3S_ACCS(M3S_GN_POINTS, 128, 5, 3, false);
             } else if (impl == 2) {
                 if (gp->mode == M3S_GN_RAYS) M3S_ACCS(M3S_GN_RAYS, 128, 4, 4, true);
                 else M3S_ACCS(M3S_GN_POINTS, 128, 4, 4, true);
