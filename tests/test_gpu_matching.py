@@ -173,6 +173,26 @@ def test_prep_and_tail_vs_oracle(K, oracle, synth):
     assert np.array_equal(idx, idx_o) and np.array_equal(valid, valid_o)
 
 
+@pytest.mark.parametrize("hw", [(40, 56), (8, 32), (9, 36), (37, 52), (3, 4), (1, 8), (50, 70), (16, 33)])
+def test_prep_shapes_vs_oracle(K, oracle, synth, hw):
+    """prep through the tiled kernel (32 x 8 tiles, shared halo of unit rays, float4 row stores):
+    full and partial tiles in x and y, single-row / 4-pixel-wide frames, and W % 4 != 0 shapes that
+    take the one-thread-per-pixel kernel -- all bit-identical to the oracle, B = 2, with and without
+    idx_init (incl. negative indices: python floor semantics)."""
+    h, w = hw
+    rng = np.random.default_rng(h * 100 + w)
+    X11 = rng.normal(size=(2, h, w, 3)).astype(np.float32)
+    X11[..., 2] += 3.0
+    X21 = rng.normal(size=(2, h * w, 3)).astype(np.float32)
+    X21[0, 0] = 0.0   # zero vector: 0 / sqrt(1e-10)
+    idx0 = rng.integers(-h * w, h * w, (2, h * w)).astype(np.int32)
+    for idx in (None, idx0):
+        got = K.prep_for_iter_proj(X11, X21.reshape(2, h, w, 3), idx)
+        ref = oracle.prep_for_iter_proj(X11, X21.reshape(2, h, w, 3), idx)
+        for a, b in zip(got, ref):
+            assert a.shape == b.shape and np.array_equal(a, b)
+
+
 @pytest.mark.parametrize("key", ["r3_d0", "r3_d2", "r1_d1", "r2_d3"])
 def test_refine_golden_dyadic(K, golden, key):
     g = golden("refine_dyadic")
