@@ -747,6 +747,10 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
+__device__ __forceinline__ void l2_prefetch(const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+
 template <int TPB, int STAGES>
 struct StreamCfg {
     static constexpr int kPts = TPB * 4;               // points per stage (4 per thread)
@@ -817,6 +821,14 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
         bulk_g2s(base + Cfg::kOffI, ide + g0, cnt * 4u, bar);
         bulk_g2s(base + Cfg::kOffC, Cj + g0, cnt * 4u, bar);
         bulk_g2s(base + Cfg::kOffV, ve + g0, cnt, bar);
+#ifdef M3S_ACCS_L2PF   // L2 prefetch of the stage M3S_ACCS_L2PF trips further on: measured SLOWER (8: 1.246, 16: 1.251 vs 1.201 ms)
+        const long long gp = g0 + (long long)M3S_ACCS_L2PF * Cfg::kPts;
+        if (gp < n1) {
+            const uint32_t c2 = (uint32_t)min((long long)Cfg::kPts, n1 - gp);
+            l2_prefetch(Xj + 3 * gp, c2 * 12u); l2_prefetch(Qe + gp, c2 * 4u);
+            l2_prefetch(ide + gp, c2 * 4u); l2_prefetch(Cj + gp, c2 * 4u); l2_prefetch(ve + gp, c2);
+        }
+#endif
     };
 
     if (tid == 0) {
