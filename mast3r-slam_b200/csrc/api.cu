@@ -93,10 +93,18 @@ M3S_API int m3s_match_iterative_proj(const float* X11, const float* X21, const f
     int32_t* p1 = reinterpret_cast<int32_t*>(w); w += align_up(T * 2 * 4);
     uint8_t* vproj = reinterpret_cast<uint8_t*>(w); w += align_up(T);
     void* ip_ws = w;
-    int rc = m3s_prep_iter_proj(X11, X21, idx_init, rays, pts, p_init, B, H, W, stream);
-    if (rc) return rc;
-    rc = m3s_iter_proj(rays, pts, p_init, p, vproj, B, H, W, N, max_iter, lambda_init,
-                       convergence_thresh, ip_ws, m3s_iter_proj_workspace_bytes(max_iter), stream);
+    // prep fused into the iter_proj tile kernel (the ray image never reaches HBM) is
+    // opt-in (M3S_MATCH_FUSED=1: measured slower on B200, see match_exact.cu); otherwise, and for the
+    // shapes the fused kernel does not take, the two separate kernels run
+    int rc = m3s::iter_proj_fused(X11, X21, idx_init, p, vproj, B, H, W, max_iter, lambda_init,
+                                  convergence_thresh, ip_ws, m3s_iter_proj_workspace_bytes(max_iter),
+                                  stream);
+    if (rc == M3S_ERR_UNSUPPORTED) {
+        rc = m3s_prep_iter_proj(X11, X21, idx_init, rays, pts, p_init, B, H, W, stream);
+        if (rc) return rc;
+        rc = m3s_iter_proj(rays, pts, p_init, p, vproj, B, H, W, N, max_iter, lambda_init,
+                           convergence_thresh, ip_ws, m3s_iter_proj_workspace_bytes(max_iter), stream);
+    }
     if (rc) return rc;
     if (radius > 0) {
         rc = m3s_refine_matches_f32(D11, D21, p, p1, B, H, W, D, N, radius, dilation_max, stream);

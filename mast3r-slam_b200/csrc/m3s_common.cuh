@@ -39,4 +39,11 @@ int sm_count_current();
 
 static inline cudaStream_t as_stream(m3s_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
+// prep_for_iter_proj + iter_proj fused into one kernel (match_exact.cu); device pointers, p_out
+// [B,H*W,2] f32, valid_out [B,H*W] u8.  M3S_ERR_UNSUPPORTED => use the separate entry points.
+int iter_proj_fused(const float* X11, const float* X21, const int32_t* idx_init, float* p_out,
+                    uint8_t* valid_out, int B, int H, int W, int max_iter, float lambda_init,
+                    float convergence_thresh, void* workspace, size_t workspace_bytes,
+                    m3s_stream_t stream);
+
 }  // namespace m3s

@@ -400,3 +400,23 @@ def test_full_size_config2_batch_properties(K, oracle, synth):
         i1, v1 = K.match_iterative_proj_device(ps["X11"][b:b + 1], ps["X21"][b:b + 1], ps["D11"][b:b + 1],
                                                ps["D21"][b:b + 1])
         assert np.array_equal(i1.cpu().numpy(), idx[b:b + 1]) and np.array_equal(v1.cpu().numpy(), valid[b:b + 1])
+
+
+@pytest.mark.parametrize("hw", [(48, 64), (37, 52), (50, 70)])
+def test_match_fused_prep_path(K, oracle, synth, monkeypatch, hw):
+    """M3S_MATCH_FUSED=1: prep_for_iter_proj computed inside the iter_proj tile kernel (unit rays of
+    the window halo in shared memory, gradients as differences, no ray image in HBM): the whole
+    match_iterative_proj must stay bit-identical to the oracle, with and without idx_init, also for
+    partial tiles, W % 4 != 0 and starts that leave the window (global fallback from X11)."""
+    monkeypatch.setenv("M3S_MATCH_FUSED", "1")
+    h, w = hw
+    ps = [synth.make_pair(31 + i, h, w, 24, "dyadic") for i in range(2)]
+    a = [np.stack([q[k] for q in ps]) for k in ("X11", "X21", "D11", "D21")]
+    idx, valid = K.match_iterative_proj_device(*a)
+    idx_o, valid_o = oracle.match_iterative_proj(*a)
+    assert np.array_equal(idx, idx_o) and np.array_equal(valid, valid_o)
+    rng = np.random.default_rng(h)
+    idx0 = rng.integers(-h * w, h * w, (2, h * w)).astype(np.int32)   # incoherent starts: fallback path
+    g = K.match_iterative_proj_device(*a, idx0)
+    r = oracle.match_iterative_proj(*a, idx0)
+    assert np.array_equal(g[0], r[0]) and np.array_equal(g[1], r[1])
