@@ -95,6 +95,14 @@ int m3s_match_tail(const float* X11, const float* X21, const int32_t* p1,
                    const uint8_t* valid_proj, int32_t* idx_out, uint8_t* valid_out, int B, int H,
                    int W, float dist_thresh, m3s_stream_t stream);
 
+/* Replaces match_simple (matching.py:41-90), the route matching.match takes under the reference's
+ * default configuration (config.py:65 use_simple=True): idx = idx_init (identity when NULL),
+ * valid = ||X11[idx] - X21|| < dist_thresh.  X11, X21 [B,H,W,3]; idx_init [B,H*W] i32 or NULL
+ *   -> idx_out [B,H*W] i32, valid_out [B,H*W] u8 (viewed as [B,H*W,1] by the caller).
+ * An index outside [0, H*W) gives valid = 0 (the reference's gather is undefined there). */
+int m3s_match_simple(const float* X11, const float* X21, const int32_t* idx_init, int32_t* idx_out,
+                     uint8_t* valid_out, int B, int H, int W, float dist_thresh, m3s_stream_t stream);
+
 /* Whole match_iterative_proj (matching.py:339-461) on device-resident inputs:
  * prep -> iter_proj -> trunc -> refine_matches -> tail, intermediates in `workspace`.
  *   X11, X21 [B,H,W,3]; D11, D21 [B,H,W,D]; idx_init [B,H*W] i32 or NULL

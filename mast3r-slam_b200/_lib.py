@@ -56,6 +56,7 @@ SIGNATURES = {
     "m3s_refine_matches": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "m3s_refine_matches_f32": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "m3s_match_tail": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
+    "m3s_match_simple": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
     "m3s_match_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "m3s_match_iterative_proj": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f,
                                       _f, _i, _i, _f, _vp, _sz, _vp]),

@@ -114,10 +114,18 @@ class FactorGraph:
       unique list (identity when every keyframe is in the graph, the reference's implicit assumption).
     """
 
-    def __init__(self, frames: KeyframeStore, K=None, img_size=None, cfg=None, capacity: int = 32):
+    def __init__(self, frames: KeyframeStore, K=None, img_size=None, cfg=None, capacity: int = 32,
+                 calib_img_size_order: str = "reference"):
         self.frames = frames
         self.K = K
         self.img_size = img_size  # (H, W), needed by solve_GN_calib
+        # The reference hands (H, W) = frame.img.shape[1:3] (global_opt.py:226) to gauss_newton_calib,
+        # which unpacks it as (width, height) (gauss_newton_calib.py:75): on non-square images the
+        # border gate compares u against H and v against W.  "reference" reproduces that (pinned by
+        # tests/golden/mlx_graph.npz); "wh" passes the geometrically intended (W, H).
+        if calib_img_size_order not in ("reference", "wh"):
+            raise ValueError("calib_img_size_order must be 'reference' or 'wh'")
+        self.calib_img_size_order = calib_img_size_order
         self.cfg = cfg or get_config()["local_opt"]
         self.device = frames.device
         self._e = 0  # undirected edges stored
@@ -244,7 +252,8 @@ class FactorGraph:
         ii, jj, idx, valid, Q = self._prep_two_way_edges()
         ii, jj = self._rows(uniq, ii, jj)
         h, w = self.img_size
-        out = solve_GN_calib(T, Xs, Cs, self.K, ii, jj, idx, valid, Q, (w, h), self.cfg)
+        size = (h, w) if self.calib_img_size_order == "reference" else (w, h)
+        out = solve_GN_calib(T, Xs, Cs, self.K, ii, jj, idx, valid, Q, size, self.cfg)
         self.frames.update_T_WCs(out[pin:], uniq[pin:])
 
 

@@ -234,6 +234,23 @@ def match_tail(X11, X21, p1_int, valid_proj, dist_thresh: float = 0.1):
     return _out(idx, as_np), _out(valid, as_np)
 
 
+def match_simple(X11, X21, idx_init=None, dist_thresh: float = 0.1):
+    """matching.py:41-90 (the reference's default route) -> (idx [B,N] i32, valid [B,N,1] bool)."""
+    as_np = _wants_numpy(X11, X21)
+    dev = _device(X11, X21, idx_init)
+    with torch.cuda.device(dev):
+        X11d, X21d = _dev(X11, torch.float32, dev), _dev(X21, torch.float32, dev)
+        b, h, w = X21d.shape[:3]
+        idx0 = None if idx_init is None else _dev(idx_init, torch.int32, dev).reshape(b, h * w)
+        idx = torch.empty((b, h * w), dtype=torch.int32, device=dev)
+        valid = torch.empty((b, h * w), dtype=torch.uint8, device=dev)
+        _lib.check(_lib.load().m3s_match_simple(
+            _ptr(X11d), _ptr(X21d), _ptr(idx0) if idx0 is not None else None, _ptr(idx), _ptr(valid),
+            b, h, w, float(dist_thresh), _stream(dev)), "match_simple")
+        valid = valid.view(torch.bool)[:, :, None]
+    return _out(idx, as_np), _out(valid, as_np)
+
+
 def match_iterative_proj_device(X11, X21, D11, D21, idx_init=None, max_iter=10, lambda_init=1e-8,
                                 convergence_thresh=1e-6, radius=3, dilation_max=2, dist_thresh=0.1):
     """Whole match_iterative_proj (matching.py:339-461) as ONE C-ABI call on device tensors.

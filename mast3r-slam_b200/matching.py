@@ -7,9 +7,9 @@ numpy arrays or torch CUDA tensors, and every arithmetic step runs in the sm_100
 (one C-ABI call enqueues prep -> iter_proj -> refine -> tail; nothing is copied back in between,
 unlike matching.py:374-377, 418-431).
 
-``match_simple`` (matching.py:41-90, the reference's *default* route) is a nearest-descriptor
-shortcut outside the north-star path and is not provided: ``match`` raises if the configuration
-asks for it, instead of silently doing something else.
+``match_simple`` (matching.py:41-90) is the route ``match`` takes under the reference's *default*
+configuration (config.py:65 ``use_simple=True``): identity / initial correspondences gated by the 3-D
+distance.  It runs in ``m3s_match_simple`` (same arithmetic as the tail kernel).
 """
 from __future__ import annotations
 
@@ -30,13 +30,15 @@ def match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init=None):
         cfg["dist_thresh"])
 
 
+def match_simple(X11, X21, D11, D21, idx_1_to_2_init=None):
+    """matching.py:41-90.  D11 / D21 are accepted and unused, as in the reference."""
+    return kernels.match_simple(X11, X21, idx_1_to_2_init, get_config()["matching"]["dist_thresh"])
+
+
 def match(X11, X21, D11, D21, idx_1_to_2_init=None):
-    """matching.py:12-38: the config switch in front of match_iterative_proj."""
+    """matching.py:12-38: the config switch between match_simple (default) and match_iterative_proj."""
     if get_config().get("matching", {}).get("use_simple", True):
-        raise NotImplementedError(
-            "matching.use_simple=True selects the reference's match_simple shortcut, which is "
-            "outside the accelerated path; set matching.use_simple=False (set_config) to use "
-            "match_iterative_proj")
+        return match_simple(X11, X21, D11, D21, idx_1_to_2_init)
     return match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init)
 
 

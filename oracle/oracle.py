@@ -141,6 +141,23 @@ def match_iterative_proj(X11, X21, D11, D21, idx_init=None, max_iter=10, lambda_
     return match_tail(X11, X21, p1, vproj, dist_thresh)
 
 
+def match_simple(X11, X21, idx_init=None, dist_thresh=0.1):
+    """matching.py:41-90 (the reference's default route, config.py:65 use_simple=True): idx is the
+    initial correspondence (identity when None), valid = ||X11[idx] - X21|| < dist_thresh.  Equals the
+    match tail with p1 = lin_to_pixel(idx) and valid_proj = all-true.  -> (idx [B,N] i32, valid [B,N,1])."""
+    X11, X21 = _f32(X11), _f32(X21)
+    b, h, w, _ = X11.shape
+    n = h * w
+    if idx_init is None:
+        idx = np.ascontiguousarray(np.broadcast_to(np.arange(n, dtype=np.int32)[None], (b, n)))
+    else:
+        idx = _i32(idx_init)
+    samp = np.stack([X11.reshape(b, n, 3)[bi, idx[bi]] for bi in range(b)])
+    d = (samp - X21.reshape(b, n, 3)) ** 2
+    dist = np.sqrt((d[..., 0] + d[..., 1]) + d[..., 2])
+    return idx, (dist < np.float32(dist_thresh))[:, :, None]
+
+
 def _gn(mode, Twc, Xs, Cs, Kmat, ii, jj, idx, valid, Q, img_size, pixel_border, z_eps, sigma_a,
         sigma_b, C_thresh, Q_thresh, max_iter, delta_thresh, pin, debug=False):
     Twc, Xs = _f32(Twc), _f32(Xs)

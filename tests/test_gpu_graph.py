@@ -124,7 +124,7 @@ def test_factor_graph_solves(mods, oracle):
         store = G.KeyframeStore(n, capacity=4)
         for k in range(g["Twc"].shape[0]):
             store.append(g["Xs"][k], g["Cs"][k] * 2.0, g["Twc"][k], 2)
-        fg = G.FactorGraph(store, K=g["K4"], img_size=(h, w), cfg=cfg)
+        fg = G.FactorGraph(store, K=g["K4"], img_size=(h, w), cfg=cfg, calib_img_size_order="wh")
         ones = np.ones((len(fwd), n, 1), np.float32)
         Qf, Qb = g["Q"][fwd].reshape(-1, n, 1), g["Q"][bwd].reshape(-1, n, 1)
         # Qj = sqrt(Qii[idx] * Qji): feed Qii = 1 and Qji = Q^2 so the stored confidence equals Q

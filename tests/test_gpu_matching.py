@@ -299,8 +299,10 @@ def test_l2_match_entry_point(K, oracle, synth):
     from mast3r_slam_b200 import matching
     from mast3r_slam_b200.config import set_config
     ps = synth.make_pairs([3], 48, 64)
-    with pytest.raises(NotImplementedError):
-        matching.match(ps["X11"], ps["X21"], ps["D11"], ps["D21"])
+    # default configuration (config.py:65 use_simple=True): the match_simple route
+    idx, valid = matching.match(ps["X11"], ps["X21"], ps["D11"], ps["D21"])
+    idx_s, valid_s = oracle.match_simple(ps["X11"], ps["X21"], None)
+    assert np.array_equal(idx, idx_s) and np.array_equal(valid, valid_s) and valid.shape == valid_s.shape
     set_config({"matching": {"use_simple": False}})
     try:
         idx, valid = matching.match(ps["X11"], ps["X21"], ps["D11"], ps["D21"])
@@ -420,3 +422,23 @@ def test_match_fused_prep_path(K, oracle, synth, monkeypatch, hw):
     g = K.match_iterative_proj_device(*a, idx0)
     r = oracle.match_iterative_proj(*a, idx0)
     assert np.array_equal(g[0], r[0]) and np.array_equal(g[1], r[1])
+
+
+def test_iter_proj_very_wide_image(K, oracle):
+    """W large enough that f32(W - 1.001) == W - 1: the upper clip bound no longer keeps x0 <= W - 2,
+    so the four corners need the reference's min(x0 + 1, W - 1) (kernels.py:178-180).  Full-frame
+    query layout (N == H*W), i.e. the shape that would otherwise select the tile kernel."""
+    h, w = 2, 40000
+    assert np.float32(w - 1.001) == np.float32(w - 1)
+    rng = np.random.default_rng(5)
+    rays = rng.normal(size=(1, h, w, 9)).astype(np.float32)
+    rays[..., :3] /= np.linalg.norm(rays[..., :3], axis=-1, keepdims=True)
+    rays[..., 3:] *= 0.05
+    pts = rng.normal(size=(1, h * w, 3)).astype(np.float32)
+    pts /= np.linalg.norm(pts, axis=-1, keepdims=True)
+    p0 = np.stack([np.tile(np.arange(w, dtype=np.float32), h), np.repeat(np.arange(h, dtype=np.float32), w)], -1)[None]
+    p0[0, -64:, 0] = w - 1  # starts in the last column: x0 = W - 1 after the clip
+    p0[0, -32:, 0] = w + 3.5
+    p, v = K.iter_proj(rays, pts, p0, 3, 1e-8, 1e-6)
+    po, vo = oracle.iter_proj(rays, pts, p0, 3, 1e-8, 1e-6)
+    assert np.array_equal(p, po) and np.array_equal(v, vo)
