@@ -95,6 +95,13 @@ int m3s_match_tail(const float* X11, const float* X21, const int32_t* p1,
                    const uint8_t* valid_proj, int32_t* idx_out, uint8_t* valid_out, int B, int H,
                    int W, float dist_thresh, m3s_stream_t stream);
 
+/* Diagnostics (bench / tests): dev_counters = 3 x uint64 in device memory, or NULL to switch off
+ * (default).  While set, the tile kernels add: [0] refine_matches queries that took the global-memory
+ * scan instead of the staged window, [1] iter_proj points of tiles without a staged window, [2]
+ * iter_proj points of windowed tiles that left the window at least once.  Process-global, not
+ * thread-safe; results never depend on it. */
+int m3s_set_path_counters(unsigned long long* dev_counters);
+
 /* Replaces match_simple (matching.py:41-90), the route matching.match takes under the reference's
  * default configuration (config.py:65 use_simple=True): idx = idx_init (identity when NULL),
  * valid = ||X11[idx] - X21|| < dist_thresh.  X11, X21 [B,H,W,3]; idx_init [B,H*W] i32 or NULL
@@ -241,11 +248,17 @@ int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* params, const floa
  *           after attach and before the first accumulate, and before detach / plan destroy.
  *   detach: unmaps the peers (the rank's own region lives until the plan is destroyed; barrier
  *           after detach on all ranks before destroying plans).
- * A peer that does not publish within ~4 s marks the solve failed (m3s_gn_status) instead of
- * hanging the device.  world <= 8. */
+ *   release: tells the plan that every importer has unmapped this rank's region (call it after the
+ *           post-detach barrier).  A plan destroyed, or re-created, without it LEAKS the exported
+ *           region on purpose: freeing memory a peer process may still have mapped is undefined.
+ * After the delta test stops a solve, the remaining enqueued iterations keep running the (empty)
+ * exchange so that epochs stay consecutive across solves.  A peer that does not publish within
+ * M3S_GN_XCH_TIMEOUT_MS (environment, read at create; default 10000, 0 = wait for ever) marks the
+ * solve failed with the distinct status 2 (m3s_gn_status) instead of hanging the device.  world <= 8. */
 int m3s_gn_exchange_create(m3s_gn_plan* plan, int rank, int world, void* ipc_handle_out);
 int m3s_gn_exchange_attach(m3s_gn_plan* plan, const void* ipc_handles);
 int m3s_gn_exchange_detach(m3s_gn_plan* plan);
+int m3s_gn_exchange_release(m3s_gn_plan* plan);
 
 /* Assemble only: dense H (+ 1e-6 I, gauss_newton.py:254) and g from the per-edge blocks through
  * fixed-order lists (gauss_newton.py:222-251).  m3s_gn_solve_update calls it itself; exposed for
@@ -258,7 +271,8 @@ int m3s_gn_assemble(m3s_gn_plan* plan, m3s_stream_t stream);
 int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* params, m3s_stream_t stream);
 
 /* status_host[0] = iterations applied, [1] = 1 if stopped by the delta test, [2] = 1 if the solve
- * failed (non-finite / not positive definite), [3] = iterations attempted.  Synchronises. */
+ * failed numerically (non-finite / not positive definite) or 2 if the peer exchange timed out,
+ * [3] = iterations attempted.  Synchronises. */
 int m3s_gn_status(m3s_gn_plan* plan, int32_t* status_host, double* last_dx_norm_host,
                   m3s_stream_t stream);
 

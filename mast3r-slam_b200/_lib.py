@@ -56,6 +56,7 @@ SIGNATURES = {
     "m3s_refine_matches": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "m3s_refine_matches_f32": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "m3s_match_tail": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
+    "m3s_set_path_counters": (_i, [_vp]),
     "m3s_match_simple": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
     "m3s_match_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "m3s_match_iterative_proj": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f,
@@ -88,6 +89,7 @@ SIGNATURES = {
     "m3s_gn_exchange_create": (_i, [_vp, _i, _i, _vp]),
     "m3s_gn_exchange_attach": (_i, [_vp, _vp]),
     "m3s_gn_exchange_detach": (_i, [_vp]),
+    "m3s_gn_exchange_release": (_i, [_vp]),
     "m3s_gn_status": (_i, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_double), _vp]),
     "m3s_gauss_newton": (_i, [_vp, C.POINTER(GNParams), _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
 }

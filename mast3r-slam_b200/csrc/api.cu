@@ -32,11 +32,19 @@ int sm_count_current() {
     return cached[dev];
 }
 
+static unsigned long long* g_path_counters = nullptr;
+unsigned long long* path_counters() { return g_path_counters; }
+
 }  // namespace m3s
 
 using namespace m3s;
 
 M3S_API int m3s_version(void) { return 1; }
+
+M3S_API int m3s_set_path_counters(unsigned long long* dev_counters) {
+    g_path_counters = dev_counters;
+    return M3S_OK;
+}
 
 M3S_API const char* m3s_last_error(void) { return g_err; }
 

@@ -1066,14 +1066,21 @@ gn_edge_finalize_kernel(const Status* __restrict__ status, int mode,
                         const double* __restrict__ poses, const EdgeMeta* __restrict__ meta,
                         const double* __restrict__ partials, int nchunks, int edge_begin,
                         int edge_end, double* __restrict__ edge_blocks, const PeerTable peers) {
-    if (status->stopped | status->failed) return;
+    // After the delta test has stopped the solve (identically on every rank) the remaining enqueued
+    // iterations are no-ops -- but with the peer exchange attached they still run the push / publish
+    // protocol (with zero blocks nobody reads), so the epoch sequence has no gaps and the
+    // double-buffer argument (a rank can be at most one epoch ahead of a peer's copy) also holds
+    // across consecutive solves.  A failed solve stops exchanging: the plan is unusable anyway.
+    if (status->failed) return;
+    const bool dead = status->stopped != 0;
+    if (dead && !kPush) return;
     // kPush: the grid covers only the owned edges
     const int e = kPush ? edge_begin + (int)blockIdx.x : (int)blockIdx.x;
     const int tid = threadIdx.x;
     __shared__ double outb[kEdgeStride];
     double* out = kPush ? outb : edge_blocks + (size_t)e * kEdgeStride;
     const EdgeMeta em = meta[e];
-    const bool skip = (e < edge_begin || e >= edge_end || !em.active);
+    const bool skip = dead || (e < edge_begin || e >= edge_end || !em.active);
     if (skip) {
         if (tid < kEdgeStride) out[tid] = 0.0;
         if (!kPush) return;
@@ -1168,12 +1175,15 @@ gn_edge_finalize_kernel(const Status* __restrict__ status, int mode,
 
 // Wait until every rank has published `epoch`, then copy the receive buffer into the plan's block
 // buffer.  A rank that owns no edges publishes from here (its finalize grid is empty).  Bounded
-// spin: a dead peer turns into status->failed after ~4 s instead of a hung GPU.
+// spin (M3S_GN_XCH_TIMEOUT_MS, default 10 000; 0 = unbounded): a dead peer turns into status->failed +
+// status->xch_timeout (reported as failed == 2 by m3s_gn_status) instead of a hung GPU.
 __global__ void __launch_bounds__(256)
 gn_exchange_wait_kernel(Status* __restrict__ status, const unsigned long long* __restrict__ my_flags,
                         const double* __restrict__ recv, double* __restrict__ edge_blocks,
-                        long long count, const PeerTable peers, int publish_here) {
-    if (status->stopped | status->failed) return;
+                        long long count, const PeerTable peers, int publish_here,
+                        unsigned long long timeout_ns) {
+    if (status->failed) return;
+    const bool dead = status->stopped != 0;  // see gn_edge_finalize_kernel: keep the epochs flowing
     __shared__ int s_ok;
     const int tid = threadIdx.x;
     if (tid == 0) s_ok = 1;
@@ -1186,7 +1196,7 @@ gn_exchange_wait_kernel(Status* __restrict__ status, const unsigned long long* _
         while (ld_acquire_sys(my_flags + tid) < peers.epoch) {
             unsigned long long t1;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-            if (t1 - t0 > 4000000000ull) { s_ok = 0; break; }
+            if (timeout_ns != 0ull && t1 - t0 > timeout_ns) { s_ok = 0; break; }
             __nanosleep(100);
         }
     }
@@ -1195,6 +1205,7 @@ gn_exchange_wait_kernel(Status* __restrict__ status, const unsigned long long* _
         if (tid == 0) { atomicExch(&status->xch_timeout, 1); atomicExch(&status->failed, 1); }
         return;
     }
+    if (dead) return;
     for (long long i = (long long)blockIdx.x * blockDim.x + tid; i < count;
          i += (long long)gridDim.x * blockDim.x)
         edge_blocks[i] = recv[i];
@@ -1930,6 +1941,9 @@ struct m3s_gn_plan {
     char* xch_local = nullptr;
     char* xch_peer[kMaxPeers] = {};            // peer mappings of the same region (own = local)
     unsigned long long xch_epoch = 0;
+    unsigned long long xch_timeout_ns = 10000000000ull;
+    bool xch_exported = false;   // an IPC handle of xch_local was handed out
+    bool xch_released = true;    // every importer has unmapped it (m3s_gn_exchange_release)
 };
 
 static size_t xch_recv_bytes(const m3s_gn_plan* p) {
@@ -1948,8 +1962,13 @@ static void xch_unmap(m3s_gn_plan* p) {  // close the peer mappings, keep the lo
 }
 static void xch_free(m3s_gn_plan* p) {
     xch_unmap(p);
-    if (p->xch_local) cudaFree(p->xch_local);
+    // Freeing an IPC-exported allocation that a peer process may still have mapped is undefined
+    // behaviour.  Unless the caller confirmed (m3s_gn_exchange_release, after its own barrier) that
+    // every importer has unmapped, the region is deliberately leaked (<= 2 x E x 288 B + 128 B).
+    if (p->xch_local && (!p->xch_exported || p->xch_released)) cudaFree(p->xch_local);
     p->xch_local = nullptr;
+    p->xch_exported = false;
+    p->xch_released = true;
     p->xch_world = 0;
     cudaGetLastError();
 }
@@ -2292,7 +2311,7 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
     gn_exchange_wait_kernel<<<wgrid, 256, 0, st>>>(
         plan->status, reinterpret_cast<const unsigned long long*>(plan->xch_local + 2 * rb),
         reinterpret_cast<const double*>(plan->xch_local + (epoch & 1) * rb), plan->edge_blocks, count,
-        pt, ne == 0 ? 1 : 0);
+        pt, ne == 0 ? 1 : 0, plan->xch_timeout_ns);
     return launch_ok("gn_exchange_wait_kernel");
 }
 
@@ -2308,6 +2327,12 @@ M3S_API int m3s_gn_exchange_create(m3s_gn_plan* plan, int rank, int world, void*
     cudaIpcMemHandle_t h;
     M3S_CUDA(cudaIpcGetMemHandle(&h, plan->xch_local));
     memcpy(ipc_handle_out, &h, sizeof(h));
+    plan->xch_exported = true;
+    plan->xch_released = false;
+    if (const char* e = getenv("M3S_GN_XCH_TIMEOUT_MS")) {
+        const long long ms = atoll(e);
+        plan->xch_timeout_ns = ms <= 0 ? 0ull : (unsigned long long)ms * 1000000ull;
+    }
     plan->xch_rank = rank;
     plan->xch_world = world;
     plan->xch_epoch = 0;
@@ -2342,6 +2367,13 @@ M3S_API int m3s_gn_exchange_detach(m3s_gn_plan* plan) {
     M3S_CUDA(cudaSetDevice(plan->device));
     M3S_CUDA(cudaDeviceSynchronize());
     xch_unmap(plan);  // the local region stays allocated until the plan dies: peers may still map it
+    return M3S_OK;
+}
+
+M3S_API int m3s_gn_exchange_release(m3s_gn_plan* plan) {
+    M3S_REQUIRE(plan, "gn_exchange_release: null plan");
+    M3S_REQUIRE(!plan->xch_attached, "gn_exchange_release: detach first");
+    plan->xch_released = true;
     return M3S_OK;
 }
 
@@ -2461,7 +2493,8 @@ M3S_API int m3s_gn_status(m3s_gn_plan* plan, int32_t* status_host, double* last_
     M3S_CUDA(cudaMemcpyAsync(&s, plan->status, sizeof(Status), cudaMemcpyDeviceToHost, as_stream(stream)));
     M3S_CUDA(cudaStreamSynchronize(as_stream(stream)));
     if (status_host) {
-        status_host[0] = s.applied; status_host[1] = s.stopped; status_host[2] = s.failed;
+        status_host[0] = s.applied; status_host[1] = s.stopped;
+        status_host[2] = s.failed ? (s.xch_timeout ? 2 : 1) : 0;
         status_host[3] = s.attempted;
     }
     if (last_dx_norm_host) *last_dx_norm_host = s.last_norm;

@@ -39,6 +39,12 @@ int sm_count_current();
 
 static inline cudaStream_t as_stream(m3s_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
+// optional device counters of the tile kernels' fallback paths (m3s_set_path_counters; null = off):
+//   [0] refine_matches queries scanned from global memory instead of the staged window
+//   [1] iter_proj points of tiles that staged no window (bounding box of the starts too large)
+//   [2] iter_proj points of windowed tiles that left the window at least once
+unsigned long long* path_counters();
+
 // prep_for_iter_proj + iter_proj fused into one kernel (match_exact.cu); device pointers, p_out
 // [B,H*W,2] f32, valid_out [B,H*W] u8.  M3S_ERR_UNSUPPORTED => use the separate entry points.
 int iter_proj_fused(const float* X11, const float* X21, const int32_t* idx_init, float* p_out,

@@ -244,7 +244,7 @@ template <int D4, typename PT>
 __global__ void __launch_bounds__(kRefineThreads, 2)
 refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21,
                     const PT* __restrict__ p1, int32_t* __restrict__ p1_out, int H, int W,
-                    int radius) {
+                    int radius, unsigned long long* __restrict__ counters) {
     extern __shared__ float4 tile[];  // [kWinY][kWinX][pitch4]
     __shared__ int s_min[2], s_max[2], s_fit;
     constexpr int P4 = TiledCfg<D4>::pitch4;
@@ -417,6 +417,13 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
         }
     }
     // write-back; queries whose window is not covered by the staged tile take the global path
+    if (counters != nullptr) {
+        int ng = 0;
+#pragma unroll
+        for (int k = 0; k < kQ; ++k) ng += (ok[k] && !(use_tile && fit[k])) ? 1 : 0;
+        ng = __reduce_add_sync(0xffffffffu, ng);
+        if (lane == 0 && ng) atomicAdd(counters, (unsigned long long)ng);
+    }
 #pragma unroll
     for (int k = 0; k < kQ; ++k) {
         if (!ok[k]) continue;
@@ -443,7 +450,8 @@ int refine_dispatch(const float* D11, const float* D21, const PT* p1, int32_t* p
         M3S_CUDA(cudaFuncSetAttribute(refine_tiled_kernel<6, PT>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         const dim3 grid((W + kTileX - 1) / kTileX, (H + kTileY - 1) / kTileY, B);
-        refine_tiled_kernel<6, PT><<<grid, kRefineThreads, smem, st>>>(D11, D21, p1, p1_out, H, W, radius);
+        refine_tiled_kernel<6, PT><<<grid, kRefineThreads, smem, st>>>(D11, D21, p1, p1_out, H, W, radius,
+                                                                       path_counters());
         return launch_ok("refine_tiled_kernel");
     }
     const unsigned grid = (unsigned)((total + kRefineThreads - 1) / kRefineThreads);

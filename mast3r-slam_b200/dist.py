@@ -144,6 +144,7 @@ class ShardedGaussNewton:
             dist.barrier(group=self.group)
             self._lib.m3s_gn_exchange_detach(self.plan.handle)
             dist.barrier(group=self.group)   # every peer has unmapped before any region is freed
+            self._lib.m3s_gn_exchange_release(self.plan.handle)
             self.exchange = "closed"
 
     def _local_base(self, t, row_elems, itemsize):
@@ -177,3 +178,14 @@ class ShardedGaussNewton:
         out = torch.empty_like(Twc)
         _lib.check(lib.m3s_gn_get_poses(plan.handle, C.c_void_p(out.data_ptr()), st))
         return out
+
+    def check(self):
+        """Synchronise and raise if the last solve failed; an exchange timeout (a peer that did not
+        publish within M3S_GN_XCH_TIMEOUT_MS) is reported as such, not as a numerical failure."""
+        st = self.plan.status()
+        if st["exchange_timeout"]:
+            raise _lib.M3SError("gn peer exchange timed out waiting for a peer rank "
+                                "(M3S_GN_XCH_TIMEOUT_MS; 0 disables the bound)")
+        if st["failed"]:
+            raise _lib.M3SError("gauss-newton solve failed (non-finite or not positive definite)")
+        return st

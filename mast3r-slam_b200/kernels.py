@@ -411,7 +411,7 @@ class GNPlan:
         nrm = C.c_double(0)
         _lib.check(self._lib.m3s_gn_status(self.handle, st, C.byref(nrm), _stream(self.device)))
         return dict(applied=st[0], stopped=bool(st[1]), failed=bool(st[2]), attempted=st[3],
-                    last_dx_norm=nrm.value)
+                    last_dx_norm=nrm.value, exchange_timeout=(st[2] == 2))
 
 
 _plan_cache: "OrderedDict[tuple, GNPlan]" = OrderedDict()

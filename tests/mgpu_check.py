@@ -53,6 +53,29 @@ def main():
         assert torch.equal(single, again)
         timing[exchange] = mdist.max_over_ranks(e0.elapsed_time(e1) / 10, dev)
         sg.close()
+    # early stop (the delta test fires after a few iterations, the remaining enqueued iterations are
+    # no-ops that still run the exchange protocol): consecutive solves on ONE plan, alternating
+    # start poses, must stay bit-identical to the single-GPU solver -- the epoch / parity
+    # double-buffer must survive solves that stop at different iterations
+    Twc2 = Twc.clone()
+    Twc2[1:, :3] += 0.003
+    stop_params = kernels.make_params(_lib.GN_POINTS, 8, 1, 2e-3, 0.0, 1.5, 0.01)
+    ref_stop = [kernels.gauss_newton_points(T, Xs, Cs, g["ii"], g["jj"], idx, valid, Q, max_iter=8,
+                                            delta_thresh=2e-3) for T in (Twc, Twc2)]
+    st1 = kernels.get_plan(g["ii"], g["jj"], 24, n, 1, dev).status()
+    assert st1["stopped"] and 0 < st1["applied"] < 8, f"test graph must stop early: {st1}"
+    for exchange in ("p2p", "nccl"):
+        sg = mdist.ShardedGaussNewton(g["ii"], g["jj"], 24, n, 1, dev, eb, ee, exchange=exchange)
+        sl = (idx[eb:ee].contiguous(), valid[eb:ee].contiguous(), Q[eb:ee].contiguous())
+        for rep in range(6):
+            k = rep % 2
+            out = sg.solve(stop_params, (Twc, Twc2)[k], Xs, Cs, *sl)
+            if rep % 3 == 2:
+                torch.cuda.synchronize()   # some solves back to back, some separated
+            assert torch.equal(out, ref_stop[k]), f"rank {rank}: {exchange} early-stop solve {rep} differs"
+        st2 = sg.check()
+        assert st2["stopped"] and st2["applied"] == st1["applied"], (st1, st2)
+        sg.close()
     # a rank that owns no edges still takes part in the exchange (publishes from the wait kernel)
     eb0, ee0 = (0, e_total) if rank == 0 else (e_total, e_total)
     sg = mdist.ShardedGaussNewton(g["ii"], g["jj"], 24, n, 1, dev, eb0, ee0, exchange="p2p")
@@ -77,7 +100,8 @@ def main():
     assert np.array_equal(idx_s, idx_f[b:e]) and np.array_equal(valid_s, valid_f[b:e])
     torch.distributed.barrier()
     if rank == 0:
-        print(f"mgpu_check ok: world={world}, sharded GN (nccl and p2p exchange) bitwise == single GPU, "
+        print(f"mgpu_check ok: world={world}, sharded GN (nccl and p2p exchange) bitwise == single GPU "
+              f"(incl. 6 consecutive early-stopped solves per exchange, stop after {st1['applied']} of 8), "
               f"pairs sharded {world}x; ms per 6-iteration solve: " +
               ", ".join(f"{k} {v:.3f}" for k, v in timing.items()))
     torch.distributed.destroy_process_group()
