@@ -1450,6 +1450,57 @@ __device__ __forceinline__ void tri_inverse32(double (*L)[kNB + 1], const double
     for (int r = 0; r < kNB; ++r) out[r * kNB + lane] = x[r];
 }
 
+// Rows of X L^T = A for a 32-row block against the 32x32 factor L (shared memory), 8 threads per
+// row: lane g of a row's 8-lane group owns columns g, g+8, g+16, g+24 of the row in registers.  Per
+// column j the owner scales x_j by dinv[j] and broadcasts it inside the group (two 32-bit shuffles);
+// every lane then updates its <= 4 columns right of j.  The dependent chain of a row is 32 x (DMUL +
+// shuffle + DFMA) instead of 32 x (DMUL + up to 31 DFMAs issued by one thread).  Needs all 256
+// threads of the CTA (32 rows x 8); X is overwritten in place.
+__device__ __forceinline__ void trsm32_rows8(double (*X)[kNB + 1], double (*L)[kNB + 1],
+                                             const double* dinv, int tid) {
+    const int r = tid >> 3, g = tid & 7;
+    double x[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) x[i] = X[r][g + 8 * i];
+#pragma unroll
+    for (int j = 0; j < kNB; ++j) {
+        const int oi = j >> 3, og = j & 7;            // compile-time after unrolling
+        double xj = x[oi] * dinv[j];                  // meaningful on the owner lane only
+        xj = __shfl_sync(0xffffffffu, xj, og, 8);
+        if (g == og) x[oi] = xj;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            // column c = g + 8 i is right of j  <=>  i > oi or (i == oi and g > og)
+            if (i > oi) x[i] -= xj * L[g + 8 * i][j];
+            else if (i == oi && g > og) x[i] -= xj * L[g + 8 * i][j];
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) X[r][g + 8 * i] = x[i];
+}
+
+// W -= B B^T on the lower triangle, 2 x 2 register tiles (136 threads busy): 4 LDS.64 per 4 DFMA
+// instead of 2 per DFMA.
+__device__ __forceinline__ void syrk32_lower(double (*Wm)[kNB + 1], double (*Bm)[kNB + 1], int tid) {
+    if (tid < 136) {
+        int ti = (int)((sqrtf(8.0f * (float)tid + 1.0f) - 1.0f) * 0.5f);
+        while (ti * (ti + 1) / 2 > tid) --ti;
+        while ((ti + 1) * (ti + 2) / 2 <= tid) ++ti;
+        const int tj = tid - ti * (ti + 1) / 2;
+        const int r = 2 * ti, c = 2 * tj;
+        double s00 = 0.0, s01 = 0.0, s10 = 0.0, s11 = 0.0;
+#pragma unroll 8
+        for (int j = 0; j < kNB; ++j) {
+            const double a0 = Bm[r][j], a1 = Bm[r + 1][j], b0 = Bm[c][j], b1 = Bm[c + 1][j];
+            s00 += a0 * b0; s01 += a0 * b1; s10 += a1 * b0; s11 += a1 * b1;
+        }
+        Wm[r][c] -= s00;
+        if (c + 1 <= r) Wm[r][c + 1] -= s01;
+        Wm[r + 1][c] -= s10;
+        Wm[r + 1][c + 1] -= s11;
+    }
+}
+
 struct DiagSmem {
     double W[kNB][kNB + 1];   // block being factorised
     double L[kNB][kNB + 1];   // previous factor, then this block's factor
@@ -1485,30 +1536,36 @@ __device__ __forceinline__ void chol_diag_block(DiagSmem& sm, Status* __restrict
         __syncthreads();
         if (tid < kNB) sm.dinv[tid] = 1.0 / sm.L[tid][tid];
         __syncthreads();
-        if (tid < kNB) {
-            // row tid of B: right-looking substitution against L_{kb-1}, row in registers
-            double x[kNB];
+        if (nt == kStepThreads) {
+            trsm32_rows8(sm.Bm, sm.L, sm.dinv, tid);
+            __syncthreads();
+            syrk32_lower(sm.W, sm.Bm, tid);
+        } else {
+            if (tid < kNB) {
+                // row tid of B: right-looking substitution against L_{kb-1}, row in registers
+                double x[kNB];
 #pragma unroll
-            for (int c = 0; c < kNB; ++c) x[c] = sm.Bm[tid][c];
+                for (int c = 0; c < kNB; ++c) x[c] = sm.Bm[tid][c];
 #pragma unroll
-            for (int j = 0; j < kNB; ++j) {
-                const double xj = x[j] * sm.dinv[j];
-                x[j] = xj;
+                for (int j = 0; j < kNB; ++j) {
+                    const double xj = x[j] * sm.dinv[j];
+                    x[j] = xj;
 #pragma unroll
-                for (int c = j + 1; c < kNB; ++c) x[c] -= xj * sm.L[c][j];
+                    for (int c = j + 1; c < kNB; ++c) x[c] -= xj * sm.L[c][j];
+                }
+#pragma unroll
+                for (int c = 0; c < kNB; ++c) sm.Bm[tid][c] = x[c];
             }
-#pragma unroll
-            for (int c = 0; c < kNB; ++c) sm.Bm[tid][c] = x[c];
-        }
-        __syncthreads();
-        // W -= B B^T (lower part)
-        for (int i = tid; i < kNB * kNB; i += nt) {
-            const int r = i / kNB, c = i % kNB;
-            if (c <= r) {
-                double s = 0.0;
+            __syncthreads();
+            // W -= B B^T (lower part)
+            for (int i = tid; i < kNB * kNB; i += nt) {
+                const int r = i / kNB, c = i % kNB;
+                if (c <= r) {
+                    double s = 0.0;
 #pragma unroll 8
-                for (int j = 0; j < kNB; ++j) s += sm.Bm[r][j] * sm.Bm[c][j];
-                sm.W[r][c] -= s;
+                    for (int j = 0; j < kNB; ++j) s += sm.Bm[r][j] * sm.Bm[c][j];
+                    sm.W[r][c] -= s;
+                }
             }
         }
     }
@@ -1560,6 +1617,115 @@ union StepSmem {
     DiagSmem d;
 };
 
+// invert L_kb for the back-substitution (off the chain; the last block is inverted by its own diag CTA)
+__device__ __forceinline__ void chol_invert_block(TileSmem& sm, const double* Ldiag,
+                                                  double* __restrict__ Linv, int kb) {
+    const int tid = threadIdx.x;
+    const double* Ld = Ldiag + (size_t)kb * kNB * kNB;
+    for (int i = tid; i < kNB * kNB; i += kStepThreads) sm.D[i / kNB][i % kNB] = __ldcg(Ld + i);
+    __syncthreads();
+    if (tid < kNB) sm.dinv[tid] = 1.0 / sm.D[tid][tid];
+    __syncthreads();
+    if (tid < 32) tri_inverse32(sm.D, sm.dinv, Linv + (size_t)kb * kNB * kNB, tid);
+    __syncthreads();
+}
+
+// update tile (tr, tc) of block step kb (see chol_step_kernel).  Everything another CTA may have
+// written earlier in the same launch (persistent kernel) is read with ld.global.cg.
+__device__ __forceinline__ void chol_tile_body(TileSmem& sm, double* Hm, double* __restrict__ Lm,
+                                               const double* Ldiag, int np, int kb, int tr, int tc,
+                                               long long* __restrict__ tl) {
+    const int tid = threadIdx.x;
+    const int nblk = np / kNB;
+    const int k0 = kb * kNB;
+    const bool first = (tr == 0) && (tc == 0);
+    const bool stamp = (tl != nullptr) && first && (tid == 0);
+    if (stamp) tl_stamp(tl, (1 * nblk + kb) * 2);
+    const int base = k0 + kNB;
+    const int r0 = base + tr * kSyrkTile, c0 = base + tc * kSyrkTile;
+    const int ty = tid / 16, tx = tid % 16;  // 16 x 16 threads, 4 x 4 outputs each (strided by 16)
+    // the tile's current values first: their latency hides behind the panel solve
+    double cval[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int gr = r0 + ty + 16 * i;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int gc = c0 + tx + 16 * j;
+            cval[i][j] = (gr <= np && gc < np && gc <= gr) ? __ldcg(Hm + (size_t)gr * np + gc) : 0.0;
+        }
+    }
+    {
+        const double* Ld = Ldiag + (size_t)kb * kNB * kNB;
+        for (int i = tid; i < kNB * kNB; i += kStepThreads) sm.D[i / kNB][i % kNB] = __ldcg(Ld + i);
+    }
+    for (int i = tid; i < kSyrkTile * kNB; i += kStepThreads) {
+        const int r = i / kNB, c = i % kNB;
+        const int gr = r0 + r, gc = c0 + r;
+        sm.A[r][c] = (gr <= np) ? __ldcg(Hm + (size_t)gr * np + k0 + c) : 0.0;
+        if (tc != tr) sm.B[r][c] = (gc < np) ? __ldcg(Hm + (size_t)gc * np + k0 + c) : 0.0;
+    }
+    __syncthreads();
+    if (tid < kNB) sm.dinv[tid] = 1.0 / sm.D[tid][tid];
+    __syncthreads();
+    // panel solve: threads 0..63 take the rows of A, threads 64..127 the rows of B
+    if (tid < kSyrkTile || (tid < 2 * kSyrkTile && tc != tr)) {
+        double (*P)[kNB + 1] = (tid < kSyrkTile) ? sm.A : sm.B;
+        const int r = tid & (kSyrkTile - 1);
+        double x[kNB];
+#pragma unroll
+        for (int c = 0; c < kNB; ++c) x[c] = P[r][c];
+#pragma unroll
+        for (int j = 0; j < kNB; ++j) {
+            const double xj = x[j] * sm.dinv[j];
+            x[j] = xj;
+#pragma unroll
+            for (int c = j + 1; c < kNB; ++c) x[c] -= xj * sm.D[c][j];
+        }
+#pragma unroll
+        for (int c = 0; c < kNB; ++c) P[r][c] = x[c];
+    }
+    __syncthreads();
+    if (stamp) { tl_stamp(tl, (1 * nblk + kb) * 2 + 1); tl_stamp(tl, (2 * nblk + kb) * 2); }
+    double (*Bp)[kNB + 1] = (tc == tr) ? sm.A : sm.B;
+    if (tc == 0) {  // this tile column publishes the solved rows (the factor's block column kb)
+        for (int i = tid; i < kSyrkTile * kNB; i += kStepThreads) {
+            const int r = i / kNB, c = i % kNB;
+            if (r0 + r <= np) Lm[(size_t)(r0 + r) * np + k0 + c] = sm.A[r][c];
+        }
+    }
+    double acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+#pragma unroll 8
+    for (int k = 0; k < kNB; ++k) {
+        double a[4], b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { a[i] = sm.A[ty + 16 * i][k]; b[i] = Bp[tx + 16 * i][k]; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] += a[i] * b[j];
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int gr = r0 + ty + 16 * i;
+        if (gr > np) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int gc = c0 + tx + 16 * j;
+            if (!(gc < np && gc <= gr)) continue;
+            // block (kb+1, kb+1) belongs to the diag CTA of this launch
+            if (first && gr < base + kNB) continue;
+            Hm[(size_t)gr * np + gc] = cval[i][j] - acc[i][j];
+        }
+    }
+    if (stamp) tl_stamp(tl, (2 * nblk + kb) * 2 + 1);
+    __syncthreads();  // persistent kernel: the shared panels are reloaded by this CTA's next tile
+}
+
 // 1-D grid: block 0 = diag CTA of block kb + 1 (first, so it is dispatched first: it is the longest
 // CTA of the launch), block 1 inverts L_kb, blocks 2.. = the tiles of the trailing lower triangle,
 // row by row: tile rows 0 .. ntc-1 hold tr + 1 tiles each, a last tile row `ntc` (present when the
@@ -1583,14 +1749,7 @@ chol_step_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* _
         return;
     }
     if (blockIdx.x == 1) {
-        // invert L_kb for the back-substitution (the last block is inverted by its own diag CTA)
-        if (kb == nblk - 1) return;
-        const double* Ld = Ldiag + (size_t)kb * kNB * kNB;
-        for (int i = tid; i < kNB * kNB; i += kStepThreads) sm.t.D[i / kNB][i % kNB] = Ld[i];
-        __syncthreads();
-        if (tid < kNB) sm.t.dinv[tid] = 1.0 / sm.t.D[tid][tid];
-        __syncthreads();
-        if (tid < 32) tri_inverse32(sm.t.D, sm.t.dinv, Linv + (size_t)kb * kNB * kNB, tid);
+        if (kb != nblk - 1) chol_invert_block(sm.t, Ldiag, Linv, kb);
         return;
     }
     int tr, tc;
@@ -1607,91 +1766,200 @@ chol_step_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* _
             tc = t - tr * (tr + 1) / 2;
         }
     }
-    const bool first = (tr == 0) && (tc == 0);
-    const bool stamp = (tl != nullptr) && first && (tid == 0);
-    if (stamp) tl_stamp(tl, (1 * nblk + kb) * 2);
-    const int base = k0 + kNB;
-    const int r0 = base + tr * kSyrkTile, c0 = base + tc * kSyrkTile;
-    const int ty = tid / 16, tx = tid % 16;  // 16 x 16 threads, 4 x 4 outputs each (strided by 16)
-    // the tile's current values first: their latency hides behind the panel solve
-    double cval[4][4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int gr = r0 + ty + 16 * i;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int gc = c0 + tx + 16 * j;
-            cval[i][j] = (gr <= np && gc < np && gc <= gr) ? Hm[(size_t)gr * np + gc] : 0.0;
-        }
-    }
-    {
-        const double* Ld = Ldiag + (size_t)kb * kNB * kNB;
-        for (int i = tid; i < kNB * kNB; i += kStepThreads) sm.t.D[i / kNB][i % kNB] = Ld[i];
-    }
-    for (int i = tid; i < kSyrkTile * kNB; i += kStepThreads) {
+    chol_tile_body(sm.t, Hm, Lm, Ldiag, np, kb, tr, tc, tl);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Persistent factorisation (opt-in, M3S_GN_CHOL=fused): the same right-looking blocked Cholesky as
+// above in ONE cooperative launch, as a dataflow of two roles:
+//   * CTA 0 is the CHAIN: iteration c brings diagonal block c up to date with the last block step
+//     (B = A[c,c-1] L_{c-1}^-T against the factor it still holds in shared memory, W = A[c,c] - B B^T),
+//     factorises it and publishes L_c.  It waits for ONE tile only: tile (0,0) of step c-2.
+//   * CTAs 1.. are WORKERS: the 64x64 tiles of the trailing update of step kb, dealt round-robin
+//     (chol_tile_body, shared with the step kernel); a worker step needs L_kb (flag from the chain)
+//     and all tiles of step kb-1 (barrier among the workers); the last worker inverts L_kb.
+// Every CTA is co-resident by construction (cudaLaunchCooperativeKernel).  Flags and the barrier are
+// monotonic words in global memory (zeroed by a memset before the launch): publish = fence +
+// st.release, wait = ld.acquire poll with a bound, so a lost CTA turns into status->failed instead of
+// a hung device.  Everything another CTA may have written during the launch is read with
+// ld.global.cg (L1 is not coherent across SMs).
+// ------------------------------------------------------------------------------------------------
+constexpr int kFusedThreads = 256;
+constexpr int kGridSpinLimit = 1 << 21;
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+struct FusedChainSmem {
+    double W[kNB][kNB + 1];    // block being factorised
+    double L[kNB][kNB + 1];    // the most recent factor (kept across steps: next step's B-solve)
+    double Bm[kNB][kNB + 1];   // A[kb,kb-1], then B = A[kb,kb-1] L_{kb-1}^-T
+    double dinv[kNB];          // 1 / diag of the most recent factor
+    int bad;
+};
+union FusedSmem {
+    TileSmem t;
+    FusedChainSmem c;
+};
+
+// chain CTA: factorise diagonal block kb; sm.L / sm.dinv hold L_{kb-1} on entry (kb > 0), L_kb on exit
+__device__ __forceinline__ void fused_chain_block(FusedChainSmem& sm, Status* __restrict__ status,
+                                                  const double* Hm, double* __restrict__ Lm,
+                                                  double* __restrict__ Ldiag, double* __restrict__ Linv,
+                                                  int np, int kb, long long* __restrict__ tl) {
+    const int tid = threadIdx.x;
+    const int k0 = kb * kNB;
+    const int nblk = np / kNB;
+    if (tid == 0) tl_stamp(tl, (0 * nblk + kb) * 2);
+    for (int i = tid; i < kNB * kNB; i += kFusedThreads) {
         const int r = i / kNB, c = i % kNB;
-        const int gr = r0 + r, gc = c0 + r;
-        sm.t.A[r][c] = (gr <= np) ? Hm[(size_t)gr * np + k0 + c] : 0.0;
-        if (tc != tr) sm.t.B[r][c] = (gc < np) ? Hm[(size_t)gc * np + k0 + c] : 0.0;
+        sm.W[r][c] = (c <= r) ? __ldcg(Hm + (size_t)(k0 + r) * np + k0 + c) : 0.0;
+        if (kb > 0) sm.Bm[r][c] = __ldcg(Hm + (size_t)(k0 + r) * np + (k0 - kNB) + c);
+    }
+    if (tid == 0) sm.bad = 0;
+    __syncthreads();
+    if (kb > 0) {
+        trsm32_rows8(sm.Bm, sm.L, sm.dinv, tid);
+        __syncthreads();
+        syrk32_lower(sm.W, sm.Bm, tid);
+        __syncthreads();
+    }
+    chol32_block(sm.W, sm.L, sm.dinv, &sm.bad);
+    if (sm.bad) {
+        if (tid == 0) status->chol_fail = 1;
+        return;
+    }
+    double* Ld = Ldiag + (size_t)kb * kNB * kNB;
+    for (int i = tid; i < kNB * kNB; i += kFusedThreads) {
+        const int r = i / kNB, c = i % kNB;
+        const double l = sm.L[r][c];
+        Ld[i] = l;
+        if (c <= r) Lm[(size_t)(k0 + r) * np + k0 + c] = l;
+    }
+    // the last block has no following step whose spare worker could invert it
+    if (kb == nblk - 1 && tid < 32) tri_inverse32(sm.L, sm.dinv, Linv + (size_t)kb * kNB * kNB, tid);
+    if (tid == 0) tl_stamp(tl, (0 * nblk + kb) * 2 + 1);
+}
+
+// Control words of one launch (zeroed by a memset node before it):
+//   ctl[0]  worker barrier counter (monotonic: W arrivals per step)
+//   ctl[1]  chain_done   = number of diagonal blocks factorised and published by the chain CTA
+//   ctl[2]  tile00_done  = 1 + the last step whose tile (0,0) is stored (the two blocks of the next-but-
+//                          one diagonal block's input: A[kb+2, kb+1], A[kb+2, kb+2])
+//   ctl[3]  fail_at      = 1 + index of the diagonal block whose factorisation failed (0 = none)
+// Dependencies: chain iteration c (factorise block c) needs tile (0,0) of step c-2; workers' step s
+// needs L_s (chain iteration s) and every tile of step s-1 (worker barrier).  The chain CTA therefore
+// never waits for the bulk of a trailing update, only for one tile that the first worker does first.
+__device__ __forceinline__ bool fused_wait_ge(const unsigned* p, unsigned v, const unsigned* fail_at,
+                                              unsigned fail_le, int* s_flag) {
+    // thread 0 polls; *s_flag: 1 = reached, 2 = a failed factorisation makes the wait moot, 0 = timeout
+    if (threadIdx.x == 0) {
+        int spins = 0, r = 0;
+        for (;;) {
+            if (ld_acquire_u32(p) >= v) { r = 1; break; }
+            const unsigned f = ld_acquire_u32(fail_at);
+            if (f != 0u && f <= fail_le) { r = 2; break; }
+            if (++spins > kGridSpinLimit) break;
+        }
+        *s_flag = r;
     }
     __syncthreads();
-    if (tid < kNB) sm.t.dinv[tid] = 1.0 / sm.t.D[tid][tid];
+    const int r = *s_flag;
     __syncthreads();
-    // panel solve: threads 0..63 take the rows of A, threads 64..127 the rows of B
-    if (tid < kSyrkTile || (tid < 2 * kSyrkTile && tc != tr)) {
-        double (*P)[kNB + 1] = (tid < kSyrkTile) ? sm.t.A : sm.t.B;
-        const int r = tid & (kSyrkTile - 1);
-        double x[kNB];
-#pragma unroll
-        for (int c = 0; c < kNB; ++c) x[c] = P[r][c];
-#pragma unroll
-        for (int j = 0; j < kNB; ++j) {
-            const double xj = x[j] * sm.t.dinv[j];
-            x[j] = xj;
-#pragma unroll
-            for (int c = j + 1; c < kNB; ++c) x[c] -= xj * sm.t.D[c][j];
+    return r == 1;
+}
+
+__device__ __forceinline__ void st_release_u32(unsigned* p, unsigned v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(kFusedThreads, 2)
+chol_fused_kernel(Status* __restrict__ status, double* Hm, double* __restrict__ Lm,
+                  double* __restrict__ Ldiag, double* __restrict__ Linv, int np, unsigned* ctl,
+                  long long* __restrict__ tl) {
+    // uniform over the grid: both flags are only written by earlier kernels (or, on a timeout, long
+    // after every CTA has passed this line)
+    if (status->stopped | status->failed) return;
+    __shared__ FusedSmem sm;
+    __shared__ int s_flag;
+    const int nblk = np / kNB;
+    const int tid = threadIdx.x;
+    if (blockIdx.x == 0) {
+        // ---- chain ----
+        for (int c = 0; c < nblk; ++c) {
+            if (c >= 2) {
+                if (!fused_wait_ge(ctl + 2, (unsigned)(c - 1), ctl + 3, 0u, &s_flag)) {
+                    if (tid == 0) status->failed = 1;   // timeout: a worker is lost
+                    return;
+                }
+            }
+            fused_chain_block(sm.c, status, Hm, Lm, Ldiag, Linv, np, c, tl);
+            __syncthreads();
+            if (sm.c.bad) {
+                if (tid == 0) { __threadfence(); st_release_u32(ctl + 3, (unsigned)(c + 1)); }
+                return;
+            }
+            if (tid == 0) { __threadfence(); st_release_u32(ctl + 1, (unsigned)(c + 1)); }
         }
-#pragma unroll
-        for (int c = 0; c < kNB; ++c) P[r][c] = x[c];
+        return;
     }
-    __syncthreads();
-    if (stamp) { tl_stamp(tl, (1 * nblk + kb) * 2 + 1); tl_stamp(tl, (2 * nblk + kb) * 2); }
-    double (*Bp)[kNB + 1] = (tc == tr) ? sm.t.A : sm.t.B;
-    if (tc == 0) {  // this tile column publishes the solved rows (the factor's block column kb)
-        for (int i = tid; i < kSyrkTile * kNB; i += kStepThreads) {
-            const int r = i / kNB, c = i % kNB;
-            if (r0 + r <= np) Lm[(size_t)(r0 + r) * np + k0 + c] = sm.t.A[r][c];
+    // ---- workers ----
+    const int W = (int)gridDim.x - 1, w = (int)blockIdx.x - 1;
+    for (int kb = 0; kb < nblk; ++kb) {
+        // L_kb published?  (a failed factorisation of block <= kb ends every worker at this step)
+        if (!fused_wait_ge(ctl + 1, (unsigned)(kb + 1), ctl + 3, (unsigned)(kb + 1), &s_flag)) {
+            if (s_flag == 0 && tid == 0) status->failed = 1;
+            return;
+        }
+        const int k0 = kb * kNB;
+        const int rows_below = np + 1 - (k0 + kNB);  // incl. the rhs row
+        const int trailing = np - (k0 + kNB);
+        const int ntr = (rows_below + kSyrkTile - 1) / kSyrkTile;
+        const int ntc0 = (trailing + kSyrkTile - 1) / kSyrkTile;
+        const int ntc = ntc0 > 0 ? ntc0 : 1;   // trailing == 0 (last step): one tile, the rhs row
+        const int ntri = ntc * (ntc + 1) / 2;
+        const int ntiles = (ntc0 == 0) ? 1 : ntri + ((ntr > ntc0) ? ntc0 : 0);
+        for (int t = w; t < ntiles; t += W) {
+            int tr, tc;
+            if (t >= ntri) {
+                tr = ntc;
+                tc = t - ntri;
+            } else {
+                tr = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
+                while (tr * (tr + 1) / 2 > t) --tr;
+                while ((tr + 1) * (tr + 2) / 2 <= t) ++tr;
+                tc = t - tr * (tr + 1) / 2;
+            }
+            chol_tile_body(sm.t, Hm, Lm, Ldiag, np, kb, tr, tc, tl);   // ends with __syncthreads
+            if (t == 0 && tid == 0) { __threadfence(); st_release_u32(ctl + 2, (unsigned)(kb + 1)); }
+        }
+        // the least loaded worker inverts L_kb for the back-substitution, off every chain
+        if (w == W - 1 && kb != nblk - 1) chol_invert_block(sm.t, Ldiag, Linv, kb);
+        if (kb + 1 < nblk) {
+            // worker barrier: every tile of step kb is stored before any tile of step kb + 1 starts
+            __syncthreads();
+            if (tid == 0) {
+                __threadfence();
+                atomicAdd(ctl, 1u);
+                const unsigned target = (unsigned)(kb + 1) * (unsigned)W;
+                int spins = 0, ok = 1;
+                while (ld_acquire_u32(ctl) < target) {
+                    if (++spins > kGridSpinLimit) { ok = 0; break; }
+                }
+                __threadfence();
+                s_flag = ok;
+            }
+            __syncthreads();
+            if (!s_flag) {
+                // timeout, or the other workers left at a failed factorisation: leave as well
+                if (tid == 0 && ld_acquire_u32(ctl + 3) == 0u) status->failed = 1;
+                return;
+            }
         }
     }
-    double acc[4][4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
-#pragma unroll 8
-    for (int k = 0; k < kNB; ++k) {
-        double a[4], b[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { a[i] = sm.t.A[ty + 16 * i][k]; b[i] = Bp[tx + 16 * i][k]; }
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-            for (int j = 0; j < 4; ++j) acc[i][j] += a[i] * b[j];
-    }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int gr = r0 + ty + 16 * i;
-        if (gr > np) continue;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int gc = c0 + tx + 16 * j;
-            if (!(gc < np && gc <= gr)) continue;
-            // block (kb+1, kb+1) belongs to the diag CTA of this launch
-            if (first && gr < base + kNB) continue;
-            Hm[(size_t)gr * np + gc] = cval[i][j] - acc[i][j];
-        }
-    }
-    if (stamp) tl_stamp(tl, (2 * nblk + kb) * 2 + 1);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1926,6 +2194,8 @@ struct m3s_gn_plan {
                                     // diagonal + diagonal blocks) and, in row np, y = L^-1 (-g)
     double* xsol = nullptr;         // [np] back-substitution result blocks
     int* flags = nullptr;           // [np / 32] publication flags of the back-substitution
+    unsigned* gbar = nullptr;       // grid-barrier counter of the persistent factorisation
+    int fused_grid = -1;            // CTAs of chol_fused_kernel (0 = not available, -1 = not probed)
     long long* timeline = nullptr;  // [4, np / 32, 2] globaltimer stamps (M3S_GN_TIMELINE=1), else null
     double* g = nullptr;            // [dim]
     double* dx = nullptr;           // [dim]
@@ -1978,7 +2248,7 @@ static void plan_free(m3s_gn_plan* p) {
     xch_free(p);
     if (p->graph_exec) cudaGraphExecDestroy(p->graph_exec);
     if (p->graph) cudaGraphDestroy(p->graph);
-    cudaFree(p->Lm); cudaFree(p->xsol); cudaFree(p->flags); cudaFree(p->timeline);
+    cudaFree(p->Lm); cudaFree(p->xsol); cudaFree(p->flags); cudaFree(p->gbar); cudaFree(p->timeline);
     cudaFree(p->poses); cudaFree(p->meta); cudaFree(p->partials); cudaFree(p->edge_blocks);
     cudaFree(p->blocks); cudaFree(p->list_edge); cudaFree(p->list_sign); cudaFree(p->free_kf);
     cudaFree(p->Hm); cudaFree(p->Ldiag); cudaFree(p->Linv); cudaFree(p->g); cudaFree(p->dx); cudaFree(p->status);
@@ -2114,6 +2384,7 @@ M3S_API m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii, const int32_t* jj, in
     ok = ok && cudaMalloc((void**)&p->Lm, sizeof(double) * (size_t)(p->np + 1) * std::max(p->np, 1)) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&p->xsol, sizeof(double) * std::max(p->np, kNB)) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&p->flags, sizeof(int) * nblk) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&p->gbar, 64) == cudaSuccess;
     if (const char* tlv = getenv("M3S_GN_TIMELINE")) {
         if (tlv[0] == '1') {
             ok = ok && cudaMalloc((void**)&p->timeline, sizeof(long long) * 8 * nblk) == cudaSuccess &&
@@ -2408,11 +2679,55 @@ static bool use_pdl() {
     return v;
 }
 
-// assemble + blocked Cholesky of the augmented matrix, enqueued on `st`: one launch per block step
+// Grid of the persistent factorisation: <= 2 CTAs per SM, never more than the chain CTA + the tiles of
+// step 0; 0 = use the launch-per-step path (the default, see below; also when the device cannot
+// launch cooperatively).  M3S_GN_CHOL_CTAS overrides the count (clamped to what is co-resident).
+static int fused_grid_size(m3s_gn_plan* plan) {
+    if (plan->fused_grid >= 0) return plan->fused_grid;
+    plan->fused_grid = 0;
+    // MEASURED (B200, config 5, dim 1393 = 44 block steps, profiles/r2_gn_timeline_*.txt): persistent
+    // kernel 13.3 us per block step (585 us), launch-per-step 11.4 us (502 us).  The chain CTA is
+    // not what bounds the persistent version: a worker step is tile 8 us (two CTAs share an SM) +
+    // worker barrier / flag hops 5 us, and the kernel boundary of the step path is the cheaper
+    // barrier (2.4 us).  Opt-in (M3S_GN_CHOL=fused) until the tiles are faster.
+    const char* e = getenv("M3S_GN_CHOL");
+    if (!(e && strcmp(e, "fused") == 0)) return 0;
+    int coop = 0, sms = 0, per_sm = 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, plan->device);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, plan->device);
+    if (!coop || sms <= 0 ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chol_fused_kernel, kFusedThreads, 0) != cudaSuccess ||
+        per_sm < 1) {
+        cudaGetLastError();
+        return 0;
+    }
+    const int np = plan->np;
+    const int trailing = np - kNB, rows_below = np + 1 - kNB;
+    const int ntr = (rows_below + kSyrkTile - 1) / kSyrkTile, ntc = (trailing + kSyrkTile - 1) / kSyrkTile;
+    const int ntiles0 = (ntc == 0) ? 1 : ntc * (ntc + 1) / 2 + ((ntr > ntc) ? ntc : 0);
+    int g = std::min(sms * std::min(per_sm, 2), 1 + ntiles0);
+    if (const char* e = getenv("M3S_GN_CHOL_CTAS")) {
+        const int v = atoi(e);
+        if (v >= 2) g = std::min(v, sms * per_sm);
+    }
+    plan->fused_grid = std::max(g, 2);
+    return plan->fused_grid;
+}
+
+// assemble + blocked Cholesky of the augmented matrix, enqueued on `st`: one cooperative launch
+// (chol_fused_kernel) or, as the fallback, one launch per block step
 static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
     if (int rc = m3s_gn_assemble(plan, reinterpret_cast<m3s_stream_t>(st))) return rc;
     const int np = plan->np;
     const int nblk = np / kNB;
+    if (const int grid = fused_grid_size(plan)) {
+        M3S_CUDA(cudaMemsetAsync(plan->gbar, 0, 64, st));
+        void* args[] = {&plan->status, &plan->Hm, &plan->Lm, &plan->Ldiag, &plan->Linv,
+                        const_cast<int*>(&np), &plan->gbar, &plan->timeline};
+        M3S_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(chol_fused_kernel), dim3(grid),
+                                             dim3(kFusedThreads), args, 0, st));
+        return launch_ok("chol_fused_kernel");
+    }
     chol_diag0_kernel<<<1, kStepThreads, 0, st>>>(plan->status, plan->Hm, plan->Lm, plan->Ldiag,
                                                    plan->Linv, np, plan->timeline);
     if (int rc = launch_ok("chol_diag0_kernel")) return rc;
@@ -2474,7 +2789,10 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
     if (plan->F == 0) return M3S_OK;
     cudaStream_t st = as_stream(stream);
     const int np = plan->np;
-    if (!plan->graph_exec && !plan->graph_failed && np > 2 * kNB) build_solve_graph(plan);
+    // (the cooperative launch is not captured: the graph only pays off for the ~90 launches of the
+    // launch-per-step path)
+    if (!plan->graph_exec && !plan->graph_failed && np > 2 * kNB && fused_grid_size(plan) == 0)
+        build_solve_graph(plan);
     if (plan->graph_exec) {
         M3S_CUDA(cudaGraphLaunch(plan->graph_exec, st));
     } else {
