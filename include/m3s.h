@@ -87,6 +87,22 @@ int m3s_refine_matches_f32(const float* D11, const float* D21, const float* p1, 
                            int B, int H, int W, int D, int N, int radius, int dilation_max,
                            m3s_stream_t stream);
 
+/* Metal-semantics variants: what the reference computes on its GPU path.
+ * iter_proj: shaders/iter_proj.metal:9-165 via metal_runner.py:118-196 -- all-fp32 bilinear blend,
+ *   PER-POINT early exit when its own step is < convergence_thresh, zero step when |det| < 1e-10,
+ *   clamp bound f32(W-1) - 0.001f.  No workspace (nothing global to resolve).
+ * refine_matches: shaders/refine_matches.metal:160-215 via refine_metal_runner.py:136-164 -- window
+ *   step = dilation, levels dilation_max .. 1 applied IN PLACE (each level restarts from the previous
+ *   winner), sequential fp32 score sum, initial best score -1e10f.
+ * Bit-exact against the shaders compiled as C++ with separately rounded operations
+ * (DESIGN.md s7); a NaN start position (undefined behaviour in the shader) yields valid = 0. */
+int m3s_iter_proj_metal(const float* rays, const float* pts, const float* p_init, float* p_out,
+                        uint8_t* valid_out, int B, int H, int W, int N, int max_iter,
+                        float lambda_init, float convergence_thresh, m3s_stream_t stream);
+int m3s_refine_matches_metal(const float* D11, const float* D21, const int32_t* p1, int32_t* p1_out,
+                             int B, int H, int W, int D, int N, int radius, int dilation_max,
+                             m3s_stream_t stream);
+
 /* Replaces the tail of match_iterative_proj (matching.py:438-461):
  *   gather X11 at clip(p1), valid = valid_proj & (||X11[p1] - X21|| < dist_thresh),
  *   idx = p1.x + W * p1.y.     X11, X21 [B,H,W,3]; p1 [B,H*W,2] i32; valid_proj [B,H*W] u8
@@ -172,6 +188,16 @@ int m3s_edge_confidence(const float* Qii, const float* Qji, const int32_t* idx,
 #define M3S_GN_PREC_F64 1
 #define M3S_GN_PREC_MIXED 2
 
+/* Which implementation of the reference is reproduced.
+ *   NUMPY (default): its numpy path (backends/mpsgraph/{kernels,gauss_newton*}.py) -- what its dispatcher
+ *          runs without Metal, and what the parity bar of this library is stated against.
+ *   METAL: its Metal compute shaders (backends/mpsgraph/shaders/*.metal + *_metal_runner.py): for
+ *          Gauss-Newton fp32 per-point arithmetic (the MIXED pass; calib keeps F64), the step cast to
+ *          fp32 and the fp32 retraction with dt = tau of gauss_newton.metal:255-301 on fp32-rounded
+ *          poses; for matching see m3s_iter_proj_metal / m3s_refine_matches_metal. */
+#define M3S_SEM_NUMPY 0
+#define M3S_SEM_METAL 1
+
 /* Scalars of gauss_newton_{rays,points,calib} (backends/mpsgraph/kernels.py:262-279, 325-346,
  * 396-412).  sigma_a = sigma_ray | sigma_point | sigma_pixel; sigma_b = sigma_depth (calib). */
 typedef struct m3s_gn_params {
@@ -187,7 +213,7 @@ typedef struct m3s_gn_params {
     float K4[4];          /* calib: fx, fy, cx, cy (the reference passes K as fp32) */
     int32_t precision;    /* M3S_GN_PREC_*: arithmetic of the per-point pass (reductions, H, the
                              solve and the poses are fp64 in every mode) */
-    int32_t reserved;
+    int32_t semantics;    /* M3S_SEM_*: which of the reference's two code paths is reproduced */
 } m3s_gn_params;
 
 /* Per-graph plan: the free-keyframe numbering of gauss_newton.py:70-78 (sorted unique(ii U jj),

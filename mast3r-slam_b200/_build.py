@@ -25,6 +25,7 @@ SOURCES = {
     "graph_host.cu": ["-fmad=false"],
     "host_pipeline.cu": [],
     "track.cu": ["-fmad=false"],
+    "metal_mode.cu": ["-fmad=false"],
 }
 
 

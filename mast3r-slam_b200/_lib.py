@@ -24,7 +24,7 @@ class GNParams(C.Structure):
         ("pixel_border", C.c_int32), ("img_w", C.c_int32), ("img_h", C.c_int32),
         ("sigma_a", C.c_double), ("sigma_b", C.c_double), ("C_thresh", C.c_double),
         ("Q_thresh", C.c_double), ("delta_thresh", C.c_double), ("z_eps", C.c_double),
-        ("K4", C.c_float * 4), ("precision", C.c_int32), ("reserved", C.c_int32),
+        ("K4", C.c_float * 4), ("precision", C.c_int32), ("semantics", C.c_int32),
     ]
 
 
@@ -56,6 +56,8 @@ SIGNATURES = {
     "m3s_refine_matches": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "m3s_refine_matches_f32": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "m3s_match_tail": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
+    "m3s_iter_proj_metal": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f, _f, _vp]),
+    "m3s_refine_matches_metal": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "m3s_set_path_counters": (_i, [_vp]),
     "m3s_match_simple": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
     "m3s_match_workspace_bytes": (_sz, [_i, _i, _i, _i]),

@@ -1741,9 +1741,7 @@ chol_step_kernel(Status* __restrict__ status, double* __restrict__ Hm, double* _
     asm volatile("griddepcontrol.wait;" ::: "memory");
     if (status->stopped | status->failed | status->chol_fail) return;
     __shared__ StepSmem sm;
-    const int tid = threadIdx.x;
     const int nblk = np / kNB;
-    const int k0 = kb * kNB;
     if (blockIdx.x == 0) {
         if (kb + 1 < nblk) chol_diag_block(sm.d, status, Hm, Lm, Ldiag, Linv, np, kb + 1, tl);
         return;
@@ -2006,6 +2004,42 @@ __device__ void sim3_retract_dev(const double* xi, double* T) {
     T[7] = s * T[7];
 }
 
+// Metal-semantics retraction (params.semantics == M3S_SEM_METAL): pose_update_kernel of
+// shaders/gauss_newton.metal:255-301 -- everything in fp32, the step is cast to fp32 first
+// (gn_metal_runner.py:303), and the translation is t' = R(dq) t ds + tau: dt = tau (:286), without
+// the Sim3 V-matrix coefficients of the numpy path.  The pose buffer of that path is fp32, so the
+// fp64 pose state is rounded to fp32 on every update.
+__device__ void sim3_retract_metal_dev(const double* xi, double* T) {
+    const float EPS = 1e-6f;
+    const float tau[3] = {(float)xi[0], (float)xi[1], (float)xi[2]};
+    const float om[3] = {(float)xi[3], (float)xi[4], (float)xi[5]};
+    const float sigma = (float)xi[6];
+    const float t[3] = {(float)T[0], (float)T[1], (float)T[2]};
+    const float q[4] = {(float)T[3], (float)T[4], (float)T[5], (float)T[6]};
+    const float s = (float)T[7];
+    const float th2 = (om[0] * om[0] + om[1] * om[1]) + om[2] * om[2];
+    const float th = sqrtf(th2 + EPS);
+    const float half = 0.5f * th;
+    const float imag = th2 < EPS ? 0.5f - th2 / 48.0f : sinf(half) / th;
+    const float real = th2 < EPS ? 1.0f - th2 / 8.0f : cosf(half);
+    const float dq[4] = {imag * om[0], imag * om[1], imag * om[2], real};
+    const float ds = expf(sigma);
+    // quat_mul(dq, q), gauss_newton.metal:17-24
+    const float qn[4] = {dq[3] * q[0] + dq[0] * q[3] + dq[1] * q[2] - dq[2] * q[1],
+                         dq[3] * q[1] - dq[0] * q[2] + dq[1] * q[3] + dq[2] * q[0],
+                         dq[3] * q[2] + dq[0] * q[1] - dq[1] * q[0] + dq[2] * q[3],
+                         dq[3] * q[3] - dq[0] * q[0] - dq[1] * q[1] - dq[2] * q[2]};
+    // quat_rotate(dq, t) = t + w uv + qv x uv, uv = 2 qv x t   (gauss_newton.metal:32-36)
+    const float uv[3] = {2.0f * (dq[1] * t[2] - dq[2] * t[1]), 2.0f * (dq[2] * t[0] - dq[0] * t[2]),
+                         2.0f * (dq[0] * t[1] - dq[1] * t[0])};
+    const float c2[3] = {dq[1] * uv[2] - dq[2] * uv[1], dq[2] * uv[0] - dq[0] * uv[2],
+                         dq[0] * uv[1] - dq[1] * uv[0]};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) T[k] = (double)((t[k] + dq[3] * uv[k] + c2[k]) * ds + tau[k]);
+    T[3] = (double)qn[0]; T[4] = (double)qn[1]; T[5] = (double)qn[2]; T[6] = (double)qn[3];
+    T[7] = (double)(ds * s);
+}
+
 // Dataflow back-substitution.  One CTA per 32-column block; the CTA with blockIdx i owns block
 // b = nblk-1-i, so every CTA waits only on CTAs with a smaller blockIdx (dispatched before it: no
 // deadlock even if the grid were not fully resident).  CTA b accumulates
@@ -2034,7 +2068,7 @@ gn_backsolve_update_kernel(Status* __restrict__ status, const double* __restrict
                            const int* __restrict__ free_kf, double delta_thresh,
                            double* __restrict__ xsol, int* __restrict__ flags, int epoch,
                            double* __restrict__ dx_out, double* __restrict__ poses,
-                           long long* __restrict__ tl) {
+                           long long* __restrict__ tl, int metal) {
     if (status->stopped | status->failed) return;
     const int nblk = np / kNB;
     const int b = nblk - 1 - (int)blockIdx.x;
@@ -2144,7 +2178,8 @@ gn_backsolve_update_kernel(Status* __restrict__ status, const double* __restrict
         double xi[7];
 #pragma unroll
         for (int k = 0; k < 7; ++k) xi[k] = __ldcg(xsol + 7 * f + k);
-        sim3_retract_dev(xi, poses + 8 * free_kf[f]);
+        if (metal) sim3_retract_metal_dev(xi, poses + 8 * free_kf[f]);
+        else sim3_retract_dev(xi, poses + 8 * free_kf[f]);
     }
 }
 
@@ -2518,7 +2553,9 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
         // which amplifies the fp32 rounding of X' (4e-5 px) to a 1e-5 relative deviation of the
         // update (scripts/gn_precision_report.py), and its problems are 2-keyframe tracking solves
         // (config 4) where the pass takes microseconds either way
-        if (resolve_precision(gp->precision) == M3S_GN_PREC_MIXED && gp->mode != M3S_GN_CALIB) {
+        // (Metal semantics: the per-point arithmetic of the reference's GPU kernel is fp32 -- the mixed pass)
+        if ((resolve_precision(gp->precision) == M3S_GN_PREC_MIXED || gp->semantics == M3S_SEM_METAL) &&
+            gp->mode != M3S_GN_CALIB) {
             // streamed kernel (bulk-copy ring): needs 16-point granularity everywhere
             const uintptr_t al_all = al | reinterpret_cast<uintptr_t>(valid);
             int impl = acc_impl();
@@ -2800,7 +2837,8 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
     }
     gn_backsolve_update_kernel<<<np / kNB, kBackThreads, 0, st>>>(
         plan->status, plan->Lm, plan->Linv, np, plan->dim, plan->F, plan->free_kf, gp->delta_thresh,
-        plan->xsol, plan->flags, 1, plan->dx, plan->poses, plan->timeline);
+        plan->xsol, plan->flags, 1, plan->dx, plan->poses, plan->timeline,
+        gp->semantics == M3S_SEM_METAL ? 1 : 0);
     return launch_ok("gn_backsolve_update_kernel");
 }
 

@@ -16,6 +16,7 @@ raise ``M3SError``.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from collections import OrderedDict
 
 import numpy as np
@@ -162,8 +163,32 @@ def prep_for_iter_proj(X11, X21, idx_1_to_2_init=None):
     return _out(rays, as_np), _out(pts, as_np), _out(p0, as_np)
 
 
+_semantics = os.environ.get("M3S_SEMANTICS", "numpy")
+
+
+def set_semantics(semantics: str):
+    """Which of the reference's two code paths every later call reproduces:
+    "numpy" (default; its numpy path, the parity bar) or "metal" (its Metal shaders: per-point early
+    exit and fp32 blend in iter_proj, in-place coarse-to-fine cascade in refine_matches, fp32
+    Gauss-Newton with dt = tau; include/m3s.h M3S_SEM_*).  Every operator also takes
+    ``semantics=...`` for one call.  ``use_metal`` does NOT select it: the reference's callers pass
+    use_metal=True everywhere and fall back to numpy without a GPU, which is the behaviour the
+    drop-in mirrors."""
+    global _semantics
+    if semantics not in ("numpy", "metal"):
+        raise ValueError(f"unknown semantics {semantics!r}")
+    _semantics = semantics
+
+
+def _is_metal(semantics) -> bool:
+    s = _semantics if semantics is None else semantics
+    if s not in ("numpy", "metal"):
+        raise ValueError(f"unknown semantics {s!r}")
+    return s == "metal"
+
+
 def iter_proj(rays_with_grad, pts3d_norm, p_init, max_iter: int = 10, lambda_init: float = 1e-8,
-              convergence_thresh: float = 1e-6, use_metal: bool = True):
+              convergence_thresh: float = 1e-6, use_metal: bool = True, semantics=None):
     """kernels.py:107-148 -> (p_final [B,N,2] f32, valid [B,N] bool)."""
     as_np = _wants_numpy(rays_with_grad, pts3d_norm, p_init)
     dev = _device(rays_with_grad, pts3d_norm, p_init)
@@ -180,6 +205,11 @@ def iter_proj(rays_with_grad, pts3d_norm, p_init, max_iter: int = 10, lambda_ini
         if b * n == 0:
             return _out(p, as_np), _out(valid.view(torch.bool), as_np)
         lib = _lib.load()
+        if _is_metal(semantics):
+            _lib.check(lib.m3s_iter_proj_metal(_ptr(rays), _ptr(pts), _ptr(p0), _ptr(p), _ptr(valid), b, h,
+                                               w, n, int(max_iter), float(lambda_init),
+                                               float(convergence_thresh), _stream(dev)), "iter_proj_metal")
+            return _out(p, as_np), _out(valid.view(torch.bool), as_np)
         nb = lib.m3s_iter_proj_workspace_bytes(int(max_iter))
         ws = _workspace(dev, nb)
         _lib.check(lib.m3s_iter_proj(_ptr(rays), _ptr(pts), _ptr(p0), _ptr(p), _ptr(valid), b, h, w,
@@ -190,7 +220,8 @@ def iter_proj(rays_with_grad, pts3d_norm, p_init, max_iter: int = 10, lambda_ini
     return _out(p, as_np), _out(valid, as_np)
 
 
-def refine_matches(D11, D21, p1, radius: int = 3, dilation_max: int = 0, use_metal: bool = True):
+def refine_matches(D11, D21, p1, radius: int = 3, dilation_max: int = 0, use_metal: bool = True,
+                   semantics=None):
     """kernels.py:463-493 -> p1_refined [B,N,2] int32.  p1 may be integer or float (truncated)."""
     as_np = _wants_numpy(D11, D21, p1)
     dev = _device(D11, D21, p1)
@@ -208,7 +239,12 @@ def refine_matches(D11, D21, p1, radius: int = 3, dilation_max: int = 0, use_met
         out = torch.empty((b, n, 2), dtype=torch.int32, device=dev)
         if b * n == 0:
             return _out(out, as_np)
-        fn = _lib.load().m3s_refine_matches_f32 if is_float else _lib.load().m3s_refine_matches
+        if _is_metal(semantics):
+            if is_float:
+                p1d = p1d.to(torch.int32)   # p1.astype(np.int32), refine_metal_runner.py:120
+            fn = _lib.load().m3s_refine_matches_metal
+        else:
+            fn = _lib.load().m3s_refine_matches_f32 if is_float else _lib.load().m3s_refine_matches
         _lib.check(fn(_ptr(D11d), _ptr(D21d), _ptr(p1d), _ptr(out), b, h, w, d, n, int(radius),
                       int(dilation_max), _stream(dev)), "refine_matches")
     return _out(out, as_np)
@@ -447,9 +483,12 @@ def set_gn_precision(precision):
 
 
 def make_params(mode, max_iter, pin, delta_thresh, C_thresh, Q_thresh, sigma_a, sigma_b=1.0,
-                K=None, img_size=(0, 0), pixel_border=0, z_eps=0.0, precision=None) -> GNParams:
-    """``precision``: None / "default", "f64" or "mixed" (include/m3s.h, M3S_GN_PREC_*)."""
+                K=None, img_size=(0, 0), pixel_border=0, z_eps=0.0, precision=None,
+                semantics=None) -> GNParams:
+    """``precision``: None / "default", "f64" or "mixed" (include/m3s.h, M3S_GN_PREC_*);
+    ``semantics``: None (module setting), "numpy" or "metal" (M3S_SEM_*)."""
     p = GNParams()
+    p.semantics = 1 if _is_metal(semantics) else 0
     if precision is None:
         precision = _gn_precision
     p.precision = {None: _lib.GN_PREC_DEFAULT, "default": _lib.GN_PREC_DEFAULT,
@@ -518,21 +557,23 @@ def _gauss_newton(params_fn, Twc, Xs, Cs, ii, jj, idx, valid, Q, pin):
 def gauss_newton_rays(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_ray: float = 0.003,
                       sigma_dist: float = 10.0, C_thresh: float = 0.0, Q_thresh: float = 1.5,
                       max_iter: int = 10, delta_thresh: float = 1e-4, pin: int = 1,
-                      use_metal: bool = True):
+                      use_metal: bool = True, semantics=None):
     """kernels.py:262-322.  ``sigma_dist`` is accepted and unused, as in the reference
     (gauss_newton.py:52)."""
     return _gauss_newton(
-        lambda: make_params(_lib.GN_RAYS, max_iter, pin, delta_thresh, C_thresh, Q_thresh, sigma_ray),
+        lambda: make_params(_lib.GN_RAYS, max_iter, pin, delta_thresh, C_thresh, Q_thresh, sigma_ray,
+                            semantics=semantics),
         Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, pin)
 
 
 def gauss_newton_points(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_point: float = 0.01,
                         C_thresh: float = 0.0, Q_thresh: float = 1.5, max_iter: int = 10,
-                        delta_thresh: float = 1e-4, pin: int = 1, use_metal: bool = True):
+                        delta_thresh: float = 1e-4, pin: int = 1, use_metal: bool = True,
+                        semantics=None):
     """kernels.py:396-455."""
     return _gauss_newton(
         lambda: make_params(_lib.GN_POINTS, max_iter, pin, delta_thresh, C_thresh, Q_thresh,
-                            sigma_point),
+                            sigma_point, semantics=semantics),
         Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, pin)
 
 
@@ -540,9 +581,10 @@ def gauss_newton_calib(Twc, Xs, Cs, K, ii, jj, idx_ii2jj, valid_match, Q, img_si
                        pixel_border: int = 0, z_eps: float = 0.0, sigma_pixel: float = 1.0,
                        sigma_depth: float = 0.1, C_thresh: float = 0.0, Q_thresh: float = 1.5,
                        max_iter: int = 10, delta_thresh: float = 1e-4, pin: int = 1,
-                       use_metal: bool = True):
+                       use_metal: bool = True, semantics=None):
     """kernels.py:325-393."""
     return _gauss_newton(
         lambda: make_params(_lib.GN_CALIB, max_iter, pin, delta_thresh, C_thresh, Q_thresh,
-                            sigma_pixel, sigma_depth, K, img_size, pixel_border, z_eps),
+                            sigma_pixel, sigma_depth, K, img_size, pixel_border, z_eps,
+                            semantics=semantics),
         Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, pin)

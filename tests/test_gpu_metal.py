@@ -1,0 +1,127 @@
+"""Metal-semantics mode on the GPU: m3s_iter_proj_metal / m3s_refine_matches_metal
+bit-exact against the reference's shaders compiled as C++ (committed goldens + fresh inputs through
+oracle/_ref when the library travelled), Gauss-Newton with params.semantics = METAL within a stated
+tolerance of the Metal runner restatement."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def load(name):
+    return np.load(os.path.join(HERE, "golden", name + ".npz"))
+
+
+@pytest.fixture(scope="module")
+def K():
+    import torch
+    assert torch.cuda.is_available()
+    from mast3r_slam_b200 import kernels
+    return kernels
+
+
+@pytest.fixture(scope="module")
+def mo():
+    from oracle import metal_oracle
+    return metal_oracle if metal_oracle.available() else None
+
+
+def test_iter_proj_metal_goldens(K):
+    g = load("metal_match")
+    for it in (1, 10):
+        p, v = K.iter_proj(g["rnd_rays"], g["rnd_pts"], g["rnd_p0"], it, 1e-8, 1e-6, semantics="metal")
+        assert np.array_equal(p, g[f"rnd_p_{it}"]) and np.array_equal(v, g[f"rnd_valid_{it}"])
+    for tag, it, th in (("a", 10, 1e-6), ("b", 10, 2e-2), ("c", 3, 1e-6)):
+        p, v = K.iter_proj(g["scn_rays"], g["scn_pts"], g["scn_p0"], it, 1e-8, th, semantics="metal")
+        assert np.array_equal(p, g[f"scn_p_{tag}"]) and np.array_equal(v, g[f"scn_valid_{tag}"])
+
+
+def test_refine_metal_goldens(K):
+    g = load("metal_match")
+    for r, dm in ((3, 1), (3, 2), (2, 5), (1, 0)):
+        out = K.refine_matches(g["ref_D11"], g["ref_D21"], g["ref_p1"], r, dm, semantics="metal")
+        assert np.array_equal(out, g[f"ref_p1_r{r}_d{dm}"])
+    out = K.refine_matches(g["ref16_D11"], g["ref16_D21"], g["ref16_p1"], 3, 2, semantics="metal")
+    assert np.array_equal(out, g["ref16_out"])
+    out = K.refine_matches(g["ref10_D11"], g["ref10_D21"], g["ref10_p1"], 2, 3, semantics="metal")
+    assert np.array_equal(out, g["ref10_out"])
+
+
+def test_metal_matching_fresh_inputs_full_frame(K, mo):
+    """full-frame pair through prep -> iter_proj -> refine in Metal semantics vs the shaders run on the host"""
+    if mo is None:
+        pytest.skip("oracle/_ref/libm3s_metal_ref.so did not travel")
+    from mast3r_slam_b200 import synth
+    ps = synth.make_pairs([7, 8], 96, 128, 24, "unit")
+    rays, pts, p0 = K.prep_for_iter_proj(ps["X11"], ps["X21"], None)
+    p, v = K.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6, semantics="metal")
+    po, vo = mo.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6)
+    assert np.array_equal(p, po) and np.array_equal(v, vo)
+    D21 = ps["D21"].reshape(2, -1, 24)
+    for dm in (1, 3):
+        out = K.refine_matches(ps["D11"], D21, p, 3, dm, semantics="metal")
+        ref = mo.refine_matches(ps["D11"], D21, po.astype(np.int32), 3, dm)
+        assert np.array_equal(out, ref)
+
+
+# Tolerance of the Gauss-Newton leg: 2e-4 of the update (+ 2 fp32 ulps of a unit-scale pose entry).
+# The Metal pipeline sums fp32 per-point contributions sequentially over all points of a keyframe;
+# this library sums them pairwise / in fp64 above 32 points, so the two differ by the rounding noise
+# of the REFERENCE's own fp32 sums.  The behavioural gap to the numpy path (dt = tau) is ~1e-3 of the
+# update, 5 x above this tolerance, and is asserted to be reproduced.
+METAL_GN_REL = 2e-4
+
+
+def test_gn_metal_goldens(K):
+    g = load("metal_gn")
+    a = (g["Twc"], g["Xs"], g["Cs"], g["ii"], g["jj"], g["idx"], g["valid"], g["Q"])
+    for it in (1, 4):
+        for name, args in (("rays", a), ("points", a)):
+            out = getattr(K, f"gauss_newton_{name}")(*args, max_iter=it, semantics="metal")
+            ref = g[f"{name}_{it}"]
+            upd = np.abs(ref - g["Twc"]).max()
+            assert np.abs(out - ref).max() <= METAL_GN_REL * upd + 2.4e-7, (name, it, np.abs(out - ref).max(), upd)
+        out = K.gauss_newton_calib(g["Twc"], g["Xs"], g["Cs"], g["K4"], g["ii"], g["jj"], g["idx"], g["valid"],
+                                   g["Q"], tuple(int(x) for x in g["img_size"]), sigma_depth=10.0, max_iter=it,
+                                   semantics="metal")
+        ref = g[f"calib_{it}"]
+        upd = np.abs(ref - g["Twc"]).max()
+        assert np.abs(out - ref).max() <= METAL_GN_REL * upd + 2.4e-7, ("calib", it, np.abs(out - ref).max(), upd)
+    # the mode reproduces the Metal path, not the numpy path
+    out = K.gauss_newton_rays(*a, max_iter=4, semantics="metal")
+    assert np.abs(out - g["rays_4"]).max() < 0.2 * np.abs(g["rays_4"] - g["numpy_rays_4"]).max()
+    # and the default stays numpy semantics
+    out_np = K.gauss_newton_rays(*a, max_iter=4)
+    assert np.abs(out_np - g["numpy_rays_4"]).max() < 0.2 * np.abs(g["rays_4"] - g["numpy_rays_4"]).max()
+
+
+def test_gn_metal_first_iteration_H_g(K):
+    """H and g of the first iteration (mixed per-point pass) against the Metal runner's float32-summed
+    H, g: relative 1e-4 of the largest entry"""
+    import ctypes as C
+    import torch
+    from mast3r_slam_b200 import _lib
+    g = load("metal_gn")
+    dev = torch.device("cuda", 0)
+    plan = K.GNPlan(g["ii"], g["jj"], len(g["Twc"]), g["Xs"].shape[1], 1, dev)
+    params = K.make_params(_lib.GN_RAYS, 1, 1, 1e-4, 0.0, 1.5, 0.003, semantics="metal")
+    t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a)).to(dev, dt)  # noqa: E731
+    Twc, Xs, Cs = t(g["Twc"], torch.float32), t(g["Xs"], torch.float32), t(g["Cs"], torch.float32)
+    idx, valid, Q = t(g["idx"], torch.int32), t(g["valid"].astype(np.uint8), torch.uint8), t(g["Q"], torch.float32)
+    lib = _lib.load()
+    p = lambda x: C.c_void_p(x.data_ptr())  # noqa: E731
+    _lib.check(lib.m3s_gn_set_poses(plan.handle, p(Twc), None))
+    _lib.check(lib.m3s_gn_accumulate(plan.handle, C.byref(params), p(Xs), p(Cs), p(idx), p(valid), p(Q), 0,
+                                     plan.E, None))
+    _lib.check(lib.m3s_gn_assemble(plan.handle, None))
+    torch.cuda.synchronize()
+    dim = plan.dim
+    H = plan.H().cpu().numpy()[:dim, :dim]
+    gv = plan.g().cpu().numpy()[:dim]
+    Href = g["rays_H"]
+    Hl, Hrefl = np.tril(H), np.tril(Href)   # the assembled matrix is used through its lower triangle
+    assert np.abs(Hl - Hrefl).max() <= 1e-4 * np.abs(Hrefl).max()
+    assert np.abs(gv - g["rays_g"]).max() <= 1e-4 * np.abs(g["rays_g"]).max()
