@@ -19,11 +19,28 @@ from .config import get_config
 prep_for_iter_proj = kernels.prep_for_iter_proj
 
 
-def match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init=None):
-    """matching.py:339-461.  X11, X21 [B,H,W,3]; D11, D21 [B,H,W,D]; idx_init [B,H*W] or None."""
+def match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init=None, semantics=None):
+    """matching.py:339-461.  X11, X21 [B,H,W,3]; D11, D21 [B,H,W,D]; idx_init [B,H*W] or None.
+    ``semantics="metal"`` (or kernels.set_semantics): the steps the reference runs through its Metal
+    shaders -- iter_proj (:393-405) and refine_matches (:411-416) -- take their Metal semantics; prep
+    and tail are the same MLX code on either path."""
     cfg = get_config()["matching"]
     radius = cfg.get("refine_radius", 3)
     use_refine = cfg.get("use_refine", True) and radius > 0
+    if kernels._is_metal(semantics):
+        rays, pts, p0 = kernels.prep_for_iter_proj(X11, X21, idx_1_to_2_init)
+        p, valid = kernels.iter_proj(rays, pts, p0, cfg["max_iter"], cfg["lambda_init"],
+                                     cfg["convergence_thresh"], semantics="metal")
+        b, h, w, _ = X11.shape
+        if use_refine:
+            d = D21.shape[-1]
+            p = kernels.refine_matches(D11, D21.reshape(b, h * w, d), p, radius,
+                                       cfg.get("refine_dilation", 2), semantics="metal")
+        elif hasattr(p, "astype"):
+            p = p.astype("int32")
+        else:
+            p = p.int()
+        return kernels.match_tail(X11, X21, p, valid, cfg["dist_thresh"])
     return kernels.match_iterative_proj_device(
         X11, X21, D11, D21, idx_1_to_2_init, cfg["max_iter"], cfg["lambda_init"],
         cfg["convergence_thresh"], radius if use_refine else 0, cfg.get("refine_dilation", 2),

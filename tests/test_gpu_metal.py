@@ -125,3 +125,22 @@ def test_gn_metal_first_iteration_H_g(K):
     Hl, Hrefl = np.tril(H), np.tril(Href)   # the assembled matrix is used through its lower triangle
     assert np.abs(Hl - Hrefl).max() <= 1e-4 * np.abs(Hrefl).max()
     assert np.abs(gv - g["rays_g"]).max() <= 1e-4 * np.abs(g["rays_g"]).max()
+
+
+def test_match_iterative_proj_metal_route(K, mo):
+    """matching.match_iterative_proj(semantics="metal") = prep -> Metal iter_proj -> Metal cascade
+    (config refine_dilation = 2) -> tail, against the same chain built from the oracles"""
+    if mo is None:
+        pytest.skip("oracle/_ref/libm3s_metal_ref.so did not travel")
+    from mast3r_slam_b200 import matching, synth
+    from oracle import oracle
+    ps = synth.make_pairs([11], 64, 96, 24, "unit")
+    idx, valid = matching.match_iterative_proj(ps["X11"], ps["X21"], ps["D11"], ps["D21"], semantics="metal")
+    rays, pts, p0 = oracle.prep_for_iter_proj(ps["X11"], ps["X21"], None)
+    p, v = mo.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6)
+    p1 = mo.refine_matches(ps["D11"], ps["D21"].reshape(1, -1, 24), p.astype(np.int32), 3, 2)
+    idx_o, valid_o = oracle.match_tail(ps["X11"], ps["X21"], p1, v, 0.1)
+    assert np.array_equal(idx, idx_o) and np.array_equal(valid, valid_o)
+    # and it is not what the default (numpy-semantics) route returns
+    idx_n, _ = matching.match_iterative_proj(ps["X11"], ps["X21"], ps["D11"], ps["D21"])
+    assert (idx_n != idx).any()
