@@ -1296,6 +1296,12 @@ __device__ __forceinline__ void tl_stamp(long long* tl, int slot) {
     }
 }
 
+// phase stamps inside the diag CTA (who = 0) / update tile (0,0) (who = 1) of block step kb: slot i of
+// tl[(8 + 8 who) * nblk + 8 kb + i] (thread 0 only; call after a barrier)
+__device__ __forceinline__ void tl_phase(long long* tl, int nblk, int who, int kb, int i) {
+    if (tl != nullptr && threadIdx.x == 0) tl_stamp(tl, (8 + 8 * who) * nblk + 8 * kb + i);
+}
+
 // 1 / sqrt(d) for 1e-290 < d < 1e300: hardware seed (2^-22) + two Newton steps, no special cases
 __device__ __forceinline__ double rsqrt_fast(double d) {
     double y;
@@ -1534,11 +1540,13 @@ __device__ __forceinline__ void chol_diag_block(DiagSmem& sm, Status* __restrict
             sm.Bm[i / kNB][i % kNB] = Hm[(size_t)(k0 + i / kNB) * np + (k0 - kNB) + (i % kNB)];
         }
         __syncthreads();
+        tl_phase(tl, nblk, 0, kb, 0);   // loads landed
         if (tid < kNB) sm.dinv[tid] = 1.0 / sm.L[tid][tid];
         __syncthreads();
         if (nt == kStepThreads) {
             trsm32_rows8(sm.Bm, sm.L, sm.dinv, tid);
             __syncthreads();
+            tl_phase(tl, nblk, 0, kb, 1);   // B solved
             syrk32_lower(sm.W, sm.Bm, tid);
         } else {
             if (tid < kNB) {
@@ -1570,6 +1578,7 @@ __device__ __forceinline__ void chol_diag_block(DiagSmem& sm, Status* __restrict
         }
     }
     __syncthreads();
+    tl_phase(tl, nblk, 0, kb, 2);   // W up to date
 #ifdef M3S_CHOL_WARP   // the one-warp left-looking version (A/B)
     if (tid < 32) {
         if (!chol32_warp(sm.W, sm.L, sm.dinv, sm.col, tid) && tid == 0) sm.bad = 1;
@@ -1578,6 +1587,7 @@ __device__ __forceinline__ void chol_diag_block(DiagSmem& sm, Status* __restrict
 #else
     chol32_block(sm.W, sm.L, sm.dinv, &sm.bad);
 #endif
+    tl_phase(tl, nblk, 0, kb, 3);   // factorised
     if (sm.bad) {
         if (tid == 0) status->chol_fail = 1;
         return;
@@ -1666,6 +1676,7 @@ __device__ __forceinline__ void chol_tile_body(TileSmem& sm, double* Hm, double*
         if (tc != tr) sm.B[r][c] = (gc < np) ? __ldcg(Hm + (size_t)gc * np + k0 + c) : 0.0;
     }
     __syncthreads();
+    if (first) tl_phase(tl, nblk, 1, kb, 0);   // loads landed
     if (tid < kNB) sm.dinv[tid] = 1.0 / sm.D[tid][tid];
     __syncthreads();
     // panel solve: threads 0..63 take the rows of A, threads 64..127 the rows of B
@@ -1709,6 +1720,7 @@ __device__ __forceinline__ void chol_tile_body(TileSmem& sm, double* Hm, double*
 #pragma unroll
             for (int j = 0; j < 4; ++j) acc[i][j] += a[i] * b[j];
     }
+    if (first) tl_phase(tl, nblk, 1, kb, 1);   // rank-32 products done (thread 0)
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const int gr = r0 + ty + 16 * i;
@@ -2422,8 +2434,8 @@ M3S_API m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii, const int32_t* jj, in
     ok = ok && cudaMalloc((void**)&p->gbar, 64) == cudaSuccess;
     if (const char* tlv = getenv("M3S_GN_TIMELINE")) {
         if (tlv[0] == '1') {
-            ok = ok && cudaMalloc((void**)&p->timeline, sizeof(long long) * 8 * nblk) == cudaSuccess &&
-                 cudaMemset(p->timeline, 0, sizeof(long long) * 8 * nblk) == cudaSuccess;
+            ok = ok && cudaMalloc((void**)&p->timeline, sizeof(long long) * 24 * nblk) == cudaSuccess &&
+                 cudaMemset(p->timeline, 0, sizeof(long long) * 24 * nblk) == cudaSuccess;
         }
     }
     ok = ok && cudaMalloc((void**)&p->g, sizeof(double) * std::max(p->dim, 1)) == cudaSuccess;
@@ -2457,7 +2469,7 @@ M3S_API double* m3s_gn_plan_g(m3s_gn_plan* plan) { return plan ? plan->g : nullp
 M3S_API double* m3s_gn_plan_dx(m3s_gn_plan* plan) { return plan ? plan->dx : nullptr; }
 M3S_API double* m3s_gn_plan_poses(m3s_gn_plan* plan) { return plan ? plan->poses : nullptr; }
 M3S_API long long* m3s_gn_plan_timeline(m3s_gn_plan* plan, int64_t* count_out) {
-    if (count_out) *count_out = (plan && plan->timeline) ? 8LL * std::max(plan->np / kNB, 1) : 0;
+    if (count_out) *count_out = (plan && plan->timeline) ? 24LL * std::max(plan->np / kNB, 1) : 0;
     return plan ? plan->timeline : nullptr;
 }
 

@@ -43,10 +43,13 @@ def main():
     assert ptr and n.value > 0, "timeline disabled"
     iface = {"shape": (int(n.value),), "typestr": "<i8", "data": (int(ptr), False), "version": 3, "strides": None}
     holder = type("_B", (), {"__cuda_array_interface__": iface})()
-    tl = torch.as_tensor(holder, device=dev).cpu().numpy().reshape(4, -1, 2).astype(np.float64)
-    nblk = tl.shape[1]
+    raw = torch.as_tensor(holder, device=dev).cpu().numpy().astype(np.float64)
+    nblk = raw.size // 24
+    tl = raw[: 8 * nblk].reshape(4, nblk, 2)
+    ph = raw[8 * nblk:].reshape(2, nblk, 8)
     t0 = tl[tl > 0].min()
     tl = (tl - t0) * 1e-3  # us
+    ph = np.where(ph > 0, (ph - t0) * 1e-3, np.nan)
     names = ["diag", "tile-solve", "tile-upd", "backsolve"]
     for k, nm in enumerate(names):
         d = tl[k]
@@ -57,6 +60,21 @@ def main():
     print("step  diag[start end]      panel[start end]     syrk[start end]")
     for kb in list(range(0, 6)) + list(range(20, 23)) + list(range(nblk - 3, nblk)):
         print(f"{kb:4d}  " + "   ".join(f"{tl[k, kb, 0]:8.1f} {tl[k, kb, 1]:8.1f}" for k in range(3)))
+    # phases inside the diag CTA (block kb) and inside update tile (0,0) of step kb
+    d = ph[0]
+    ks = [k for k in range(1, nblk) if not np.isnan(d[k, :4]).any()]
+    if ks:
+        seg = np.array([[d[k, 0] - tl[0, k, 0], d[k, 1] - d[k, 0], d[k, 2] - d[k, 1], d[k, 3] - d[k, 2],
+                         tl[0, k, 1] - d[k, 3]] for k in ks])
+        print("diag CTA phases, mean us over blocks 1..: load %.2f | B-solve %.2f | syrk %.2f | chol32 %.2f | store(+inv) %.2f"
+              % tuple(seg.mean(0)))
+    u = ph[1]
+    ks = [k for k in range(nblk) if not np.isnan(u[k, :2]).any()]
+    if ks:
+        seg = np.array([[u[k, 0] - tl[1, k, 0], tl[1, k, 1] - u[k, 0], u[k, 1] - tl[2, k, 0], tl[2, k, 1] - u[k, 1]]
+                        for k in ks])
+        print("tile (0,0) phases, mean us: load %.2f | panel solve %.2f | rank-32 products %.2f | store %.2f"
+              % tuple(seg.mean(0)))
     per_step = (tl[1, nblk - 1, 1] - tl[0, 0, 0]) / nblk
     print(f"factorisation: {tl[1, nblk - 1, 1] - tl[0, 0, 0]:.1f} us = {per_step:.2f} us per block step")
     b = tl[3]
