@@ -331,6 +331,10 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
             d0 += srow;
         }
     }
+    // Query descriptors are fetched HERE, after the window's cp.async are in flight.  Measured on B200
+    // (64 pairs, profiles/r2_refine_ab.txt): fetching them before the first barrier costs +2 %
+    // (1.567 vs 1.537 ms -- 24 registers live across the staging loop), and warming the L2 for the CTA
+    // one wave ahead with prefetch.global.L2 costs +11 % (1.70 ms): the prologue is not DRAM-latency bound.
     float4 q[kQ][D4];
 #pragma unroll
     for (int k = 0; k < kQ; ++k) {
