@@ -15,10 +15,10 @@
 //  * refine_tiled_kernel (full-frame matching, N == H*W, D == 24, r <= 3): the hot one.
 //    CTA = 32 x 16 queries (128 threads, 4 queries per thread stacked in y, lanes along x).  The
 //    candidate neighbourhood of the whole tile (40 x 24 pixels of D11) is staged once in shared
-//    memory (112-B pixel pitch => conflict-free LDS.128 across lanes); each candidate descriptor a
-//    thread loads is reused by up to 4 queries from registers (FFMA2 packed FMAs).  A query whose
-//    window does not fit the staged tile (incoherent flow) takes the generic global-memory path,
-//    so the result never depends on the tiling.
+//    memory (96-B pixel pitch, chunk index XOR-swizzled => conflict-free LDS.128 across lanes); each
+//    candidate descriptor a thread loads is reused by up to 4 queries from registers (FFMA2 packed
+//    FMAs).  A query whose window does not fit the staged tile (incoherent flow) takes the generic
+//    global-memory path, so the result never depends on the tiling.
 //  * refine_kernel_vec / _generic: one thread per query straight from global memory/L1 (any N, D, r).
 #include <limits.h>
 
@@ -140,16 +140,45 @@ refine_kernel_generic(const float* __restrict__ D11, const float* __restrict__ D
 // ------------------------------------------------------------------------------------------------
 // Tiled kernel.
 // ------------------------------------------------------------------------------------------------
+// Tile shape: 32 x 16 queries, 40 x 24 window, 4 warps, 2 CTAs/SM.  Pixel pitch in shared memory:
+//   default              96 B, the chunk index XOR-swizzled by bit 2 of the window column
+//   -DM3S_REFINE_PITCH112 112 B (6 chunks + 16 B pad), no swizzle (round 1)
+// (A 32 x 12 tile with 3 CTAs/SM does not work: 9 warps put 3 on one SM sub-partition, whose 16 K
+// registers then cap a thread at 168 -- the scan needs ~200 and spills: 2.45 ms.)
 constexpr int kTileX = 32, kTileY = 16, kQ = 4;      // queries per CTA: 32 x 16, 4 per thread (in y)
 constexpr int kWinX = 40, kWinY = 24;                // staged candidate window (pixels)
-constexpr int kMaxTiledRadius = 3;                   // 32 + 2*3 <= 40, 16 + 2*3 <= 24 (2 px slack)
+#if defined(M3S_REFINE_PITCH112)
+constexpr bool kSwz = false;
+#else
+constexpr bool kSwz = true;
+#endif
+constexpr int kTiledMinBlocks = 2;
+constexpr int kTiledThreads = 32 * kTileY / kQ;
+// TIMING-ONLY experiments (results are wrong): how long is the scan without the staging / query traffic?
+#ifdef M3S_REFINE_TIMING_NOSTAGE
+constexpr bool kTimingNoStage = true;
+#else
+constexpr bool kTimingNoStage = false;
+#endif
+#ifdef M3S_REFINE_TIMING_NOQ
+constexpr bool kTimingNoQ = true;
+#else
+constexpr bool kTimingNoQ = false;
+#endif
+constexpr int kMaxTiledRadius = 3;                   // 32 + 2*3 <= 40, tile rows + 2*3 <= window rows
 
 template <int D4>
 struct TiledCfg {
-    static constexpr int pitch4 = D4 + 1;                               // float4 per pixel (+16 B pad)
+    // float4 per pixel: + 16 B pad (lane stride 7 chunks: conflict-free LDS.128 across lanes), or no pad
+    // and chunk d of window column c stored in slot d ^ ((c >> 2) & 1): lanes c..c+7 then hit the
+    // eight 16-B bank groups {0,6,4,2} + d and {1,7,5,3} + d -- also conflict-free, 14 % less smem
+    static constexpr int pitch4 = kSwz ? D4 : D4 + 1;
     // + one padded row: lanes walk the warp-wide column count from their own base without a clamp,
     // so reads may run past the end of the last window row (values discarded by the column mask)
-    static constexpr size_t smem_bytes = (size_t)(kWinX * kWinY + kWinX + 4) * pitch4 * 16;
+    // (a lane's base column is <= kWinX - 7, the warp-wide column count <= 32, the software pipeline
+    // looks one pair ahead: <= 28 pixels past the end)
+    static constexpr int pad_px = kWinX + 4;
+    static constexpr size_t smem_bytes = (size_t)(kWinX * kWinY + pad_px) * pitch4 * 16;
 };
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
@@ -173,9 +202,23 @@ __device__ __forceinline__ void cp_async_wait_all() {
 // pair after the current one is fetched chunk by chunk into the registers the current pair has
 // just finished with (c[d] is dead after chunk d), so its LDS latency is covered by the remaining
 // chunks and the score epilogue -- a software pipeline without a second register buffer.
+// pointer(s) to the D4 chunks of window column `col` of a row: chunk d is e[d] for even d, o[d] for odd d
+// (e == o without the swizzle)
 template <int D4>
-__device__ __forceinline__ const float4* cand_ptr(const float4* __restrict__ row, int col) {
-    return row + col * TiledCfg<D4>::pitch4;
+struct Cand {
+    const float4* __restrict__ e;
+    const float4* __restrict__ o;
+    __device__ __forceinline__ float4 operator[](int d) const { return (d & 1) ? o[d] : e[d]; }
+};
+template <int D4>
+__device__ __forceinline__ Cand<D4> cand_ptr(const float4* __restrict__ row, int col) {
+    const float4* p = row + col * TiledCfg<D4>::pitch4;
+    if constexpr (kSwz) {
+        const int s = (col >> 2) & 1;
+        return Cand<D4>{p + s, p - s};
+    } else {
+        return Cand<D4>{p, p};
+    }
 }
 
 template <unsigned KMASK>
@@ -199,7 +242,7 @@ __device__ __forceinline__ void cand_pick(const Acc4 (&a)[kQ], int pos, unsigned
 // from n0 / n1 (the next pair) as their chunks retire
 template <int D4, unsigned KMASK, bool SECOND>
 __device__ __forceinline__ void pair_eval(float4 (&c0)[D4], float4 (&c1)[D4],
-                                          const float4* __restrict__ n0, const float4* __restrict__ n1,
+                                          const Cand<D4> n0, const Cand<D4> n1,
                                           int i, int jbits, const float4 (&q)[kQ][D4],
                                           const unsigned (&rmask)[kQ], float (&best)[kQ],
                                           int (&bpos)[kQ]) {
@@ -232,16 +275,64 @@ __device__ __forceinline__ void row_scan(const float4* __restrict__ row, const f
     for (; i + 2 < NC; i += 2)
         pair_eval<D4, KMASK, true>(c0, c1, cand_ptr<D4>(row, xb + i + 2), cand_ptr<D4>(row, xb + i + 3),
                                    i, jbits, q, rmask, best, bpos);
-    const float4* __restrict__ n0 = cand_ptr<D4>(nrow, xb);
-    const float4* __restrict__ n1 = cand_ptr<D4>(nrow, xb + 1);
+    const Cand<D4> n0 = cand_ptr<D4>(nrow, xb);
+    const Cand<D4> n1 = cand_ptr<D4>(nrow, xb + 1);
     if (i + 1 < NC)
         pair_eval<D4, KMASK, true>(c0, c1, n0, n1, i, jbits, q, rmask, best, bpos);
     else
         pair_eval<D4, KMASK, false>(c0, c1, n0, n1, i, jbits, q, rmask, best, bpos);
 }
 
+// Default scan: ONE candidate per evaluation, two register buffers (cA, cB) in ping-pong: the loads
+// of the candidate after next are issued before the current one is evaluated.  Measured on B200 (64
+// pairs, profiles/r2_refine_ab.txt): 1.459 ms against 1.529 ms for the pair evaluation of round 1
+// (row_scan, -DM3S_REFINE_PAIR) -- 169 instead of 185 instructions per two candidates and ~200
+// instead of 220 registers.  Invariant on entry and exit: cA holds column 0 of the row to scan.
+template <int D4, unsigned KMASK>
+__device__ __forceinline__ void cand_eval(const float4 (&c)[D4], int i, int jbits, const float4 (&q)[kQ][D4],
+                                          const unsigned (&rmask)[kQ], float (&best)[kQ], int (&bpos)[kQ]) {
+    Acc4 a[kQ];
+#pragma unroll
+    for (int d = 0; d < D4; ++d) {
+#pragma unroll
+        for (int k = 0; k < kQ; ++k)
+            if ((KMASK >> k) & 1u) a[k].fma4(q[k][d], c[d]);
+    }
+    cand_pick<KMASK>(a, jbits | i, 1u << i, rmask, best, bpos);
+}
+template <int D4>
+__device__ __forceinline__ void cand_load(float4 (&c)[D4], const Cand<D4> p) {
+#pragma unroll
+    for (int d = 0; d < D4; ++d) c[d] = p[d];
+}
+template <int D4, unsigned KMASK>
+__device__ __forceinline__ void row_scan_pp(const float4* __restrict__ row, const float4* __restrict__ nrow,
+                                            int xb, int NC, int j, float4 (&cA)[D4], float4 (&cB)[D4],
+                                            const float4 (&q)[kQ][D4], const unsigned (&rmask)[kQ],
+                                            float (&best)[kQ], int (&bpos)[kQ]) {
+    const int jbits = j << 16;
+    int i = 0;
+    for (; i + 2 < NC; i += 2) {
+        cand_load<D4>(cB, cand_ptr<D4>(row, xb + i + 1));
+        cand_eval<D4, KMASK>(cA, i, jbits, q, rmask, best, bpos);
+        cand_load<D4>(cA, cand_ptr<D4>(row, xb + i + 2));
+        cand_eval<D4, KMASK>(cB, i + 1, jbits, q, rmask, best, bpos);
+    }
+    if (i + 1 < NC) {
+        cand_load<D4>(cB, cand_ptr<D4>(row, xb + i + 1));
+        cand_eval<D4, KMASK>(cA, i, jbits, q, rmask, best, bpos);
+        cand_load<D4>(cA, cand_ptr<D4>(nrow, xb));
+        cand_eval<D4, KMASK>(cB, i + 1, jbits, q, rmask, best, bpos);
+    } else {
+        cand_load<D4>(cB, cand_ptr<D4>(nrow, xb));
+        cand_eval<D4, KMASK>(cA, i, jbits, q, rmask, best, bpos);
+#pragma unroll
+        for (int d = 0; d < D4; ++d) cA[d] = cB[d];
+    }
+}
+
 template <int D4, typename PT>
-__global__ void __launch_bounds__(kRefineThreads, 2)
+__global__ void __launch_bounds__(kTiledThreads, kTiledMinBlocks)
 refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21,
                     const PT* __restrict__ p1, int32_t* __restrict__ p1_out, int H, int W,
                     int radius, unsigned long long* __restrict__ counters) {
@@ -308,25 +399,32 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
         // asynchronous staging (LDGSTS, no register round trip): a window row is kWinX * D4
         // consecutive float4 in global memory; thread t copies float4 t and t + 128 of every row.
         constexpr int ROW4 = kWinX * D4;  // 240
-        const int f0 = threadIdx.x, f1 = threadIdx.x + kRefineThreads;
-        const int px0 = f0 / D4, px1 = f1 / D4;
-        const bool in0 = (wx0 + px0 >= 0) && (wx0 + px0 < W);
-        const bool in1 = (f1 < ROW4) && (wx0 + px1 >= 0) && (wx0 + px1 < W);
-        const int s0 = px0 * P4 + (f0 - px0 * D4), s1 = px1 * P4 + (f1 - px1 * D4);
-        // hoisted addressing: one 64-bit source pointer and one 32-bit shared address per copy,
+        constexpr int NCP = (ROW4 + kTiledThreads - 1) / kTiledThreads;  // copies per thread and row
+        bool in[NCP];
+        int f[NCP];
+        unsigned doff[NCP];
+#pragma unroll
+        for (int c = 0; c < NCP; ++c) {
+            f[c] = threadIdx.x + c * kTiledThreads;
+            const int px = f[c] / D4, d = f[c] - px * D4;
+            in[c] = (f[c] < ROW4) && (wx0 + px >= 0) && (wx0 + px < W);
+            doff[c] = (unsigned)(px * P4 + (kSwz ? (d ^ ((px >> 2) & 1)) : d)) * 16u;
+        }
+        // hoisted addressing: one 64-bit source pointer and one 32-bit shared address per row,
         // advanced by constant strides; only rows inside the image are visited (the per-row
         // address arithmetic of the first version was 11 % of all executed instructions, ncu s15)
         const int wy_lo = max(0, -wy0), wy_hi = min(kWinY, H - wy0);
         const size_t grow = (size_t)W * D4;  // float4 per image row
         // `src` may point before the row start when wx0 < 0; only in-image elements are touched
         const float4* __restrict__ src = img + ((long long)(wy0 + wy_lo) * W + wx0) * D4;
-        unsigned d0 = (unsigned)__cvta_generic_to_shared(tile + wy_lo * kWinX * P4 + s0);
-        const unsigned d10 = (unsigned)((s1 - s0) * 16);
+        unsigned d0 = (unsigned)__cvta_generic_to_shared(tile + wy_lo * kWinX * P4);
         constexpr unsigned srow = kWinX * P4 * 16;
 #pragma unroll 4
         for (int wy = wy_lo; wy < wy_hi; ++wy) {
-            if (in0) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d0), "l"(src + f0) : "memory");
-            if (in1) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d0 + d10), "l"(src + f1) : "memory");
+#pragma unroll
+            for (int c = 0; c < NCP; ++c)
+                if (in[c] && !kTimingNoStage)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d0 + doff[c]), "l"(src + f[c]) : "memory");
             src += grow;
             d0 += srow;
         }
@@ -342,7 +440,8 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
             const float4* __restrict__ qp =
                 reinterpret_cast<const float4*>(D21) + ((size_t)b * N + (size_t)(qy0 + k) * W + qx) * D4;
 #pragma unroll
-            for (int d = 0; d < D4; ++d) q[k][d] = __ldg(qp + d);
+            for (int d = 0; d < D4; ++d)
+                q[k][d] = kTimingNoQ ? make_float4((float)lane, (float)k, (float)d, 1.f) : __ldg(qp + d);
         } else {
 #pragma unroll
             for (int d = 0; d < D4; ++d) q[k][d] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -388,8 +487,8 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
         float4 c0[D4], c1[D4];  // the candidate pair in flight (columns i, i+1 of the current row)
         {
             const float4* __restrict__ r0 = tile + (min(yb, kWinY - 1) * kWinX) * P4;
-            const float4* __restrict__ p0 = cand_ptr<D4>(r0, xb);
-            const float4* __restrict__ p1 = cand_ptr<D4>(r0, xb + 1);
+            const Cand<D4> p0 = cand_ptr<D4>(r0, xb);
+            const Cand<D4> p1 = cand_ptr<D4>(r0, xb + 1);
 #pragma unroll
             for (int d = 0; d < D4; ++d) { c0[d] = p0[d]; c1[d] = p1[d]; }
         }
@@ -404,11 +503,15 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
             }
             const float4* __restrict__ row = tile + (min(yb + j, kWinY - 1) * kWinX) * P4;
             const float4* __restrict__ nrow = tile + (min(yb + j + 1, kWinY - 1) * kWinX) * P4;
+#ifdef M3S_REFINE_PAIR
 #define M3S_ROW(MASK) case MASK: row_scan<D4, MASK>(row, nrow, xb, NC, j, c0, c1, q, rmask, best, bpos); break
+#else
+#define M3S_ROW(MASK) case MASK: row_scan_pp<D4, MASK>(row, nrow, xb, NC, j, c0, c1, q, rmask, best, bpos); break
+#endif
             switch (kmask) {  // warp-uniform
                 case 0: {  // no query uses this row: just advance the pipeline to the next row
-                    const float4* __restrict__ p0 = cand_ptr<D4>(nrow, xb);
-                    const float4* __restrict__ p1 = cand_ptr<D4>(nrow, xb + 1);
+                    const Cand<D4> p0 = cand_ptr<D4>(nrow, xb);
+                    const Cand<D4> p1 = cand_ptr<D4>(nrow, xb + 1);
 #pragma unroll
                     for (int d = 0; d < D4; ++d) { c0[d] = p0[d]; c1[d] = p1[d]; }
                     break;
@@ -454,7 +557,7 @@ int refine_dispatch(const float* D11, const float* D21, const PT* p1, int32_t* p
         M3S_CUDA(cudaFuncSetAttribute(refine_tiled_kernel<6, PT>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         const dim3 grid((W + kTileX - 1) / kTileX, (H + kTileY - 1) / kTileY, B);
-        refine_tiled_kernel<6, PT><<<grid, kRefineThreads, smem, st>>>(D11, D21, p1, p1_out, H, W, radius,
+        refine_tiled_kernel<6, PT><<<grid, kTiledThreads, smem, st>>>(D11, D21, p1, p1_out, H, W, radius,
                                                                        path_counters());
         return launch_ok("refine_tiled_kernel");
     }
