@@ -145,14 +145,25 @@ refine_kernel_generic(const float* __restrict__ D11, const float* __restrict__ D
 //   -DM3S_REFINE_PITCH112 112 B (6 chunks + 16 B pad), no swizzle (round 1)
 // (A 32 x 12 tile with 3 CTAs/SM does not work: 9 warps put 3 on one SM sub-partition, whose 16 K
 // registers then cap a thread at 168 -- the scan needs ~200 and spills: 2.45 ms.)
-constexpr int kTileX = 32, kTileY = 16, kQ = 4;      // queries per CTA: 32 x 16, 4 per thread (in y)
-constexpr int kWinX = 40, kWinY = 24;                // staged candidate window (pixels)
+// -DM3S_REFINE_TILEY=20 -DM3S_REFINE_WINY=28: 5 warps per CTA, 2 CTAs/SM = 10 warps (A/B, see profiles/)
+#ifndef M3S_REFINE_TILEY
+#define M3S_REFINE_TILEY 16
+#endif
+#ifndef M3S_REFINE_WINY
+#define M3S_REFINE_WINY (M3S_REFINE_TILEY + 8)
+#endif
+constexpr int kTileX = 32, kTileY = M3S_REFINE_TILEY, kQ = 4;  // queries per CTA: 32 x 16, 4 per thread (in y)
+constexpr int kWinX = 40, kWinY = M3S_REFINE_WINY;            // staged candidate window (pixels)
+static_assert(kTileY % kQ == 0 && kWinY >= kTileY + 6, "refine tile shape");
 #if defined(M3S_REFINE_PITCH112)
 constexpr bool kSwz = false;
 #else
 constexpr bool kSwz = true;
 #endif
-constexpr int kTiledMinBlocks = 2;
+#ifndef M3S_REFINE_MINBLOCKS
+#define M3S_REFINE_MINBLOCKS 2
+#endif
+constexpr int kTiledMinBlocks = M3S_REFINE_MINBLOCKS;
 constexpr int kTiledThreads = 32 * kTileY / kQ;
 // TIMING-ONLY experiments (results are wrong): how long is the scan without the staging / query traffic?
 #ifdef M3S_REFINE_TIMING_NOSTAGE
@@ -390,11 +401,11 @@ refine_tiled_kernel(const float* __restrict__ D11, const float* __restrict__ D21
         nok += ok[k];
     }
     {
-        const int v = __reduce_add_sync(0xffffffffu, nfit * 1024 + nok);  // <= 128 each: no overflow
+        const int v = __reduce_add_sync(0xffffffffu, nfit * 4096 + nok);  // <= 128 each per warp, <= 1536 per CTA
         if (lane == 0) atomicAdd(&s_fit, v);
     }
     __syncthreads();
-    const bool use_tile = (s_fit >> 10) * 4 >= (s_fit & 1023);  // >= 25 % of the queries fit
+    const bool use_tile = (s_fit >> 12) * 4 >= (s_fit & 4095);  // >= 25 % of the queries fit
     if (use_tile) {
         // asynchronous staging (LDGSTS, no register round trip): a window row is kWinX * D4
         // consecutive float4 in global memory; thread t copies float4 t and t + 128 of every row.
