@@ -445,7 +445,7 @@ def main():
             f64 = gn_leg(args, rank, world, dev, peak, "f64", check=False)
             gn["pose_diff_vs_f64"] = float((gn.pop("_poses") - f64.pop("_poses")).abs().max())
             gn["gn_f64"] = {k: f64[k] for k in ("value", "ms_per_iter", "accumulate_ms",
-                                                "solve_update_ms", "roofline", "status", "precision")}
+                                                "solve_update_ms", "solve_path", "roofline", "status", "precision")}
         gn.pop("_poses", None)
         if rank == 0:
             if world == 1 and not args.no_cpu:
@@ -659,6 +659,7 @@ def gn_leg(args, rank, world, dev, peak, precision, check=True):
     alg = 9 * ne * NPIX + 16 * GN_KF * NPIX + (7 * 199) ** 2 * 8
     err0 = float(abs(g["Twc"] - g["Twc_gt"]).max())
     exchange = sg.exchange
+    solve_path = int(lib.m3s_gn_plan_factor_path(sg.plan.handle))
     sg.close()
     out = {
         "metric": "gn_iters_per_s (gauss_newton_points, 200 KF / 1000 directed edges, 196608 pts/KF)",
@@ -668,6 +669,8 @@ def gn_leg(args, rank, world, dev, peak, precision, check=True):
                      "nccl": "NCCL all-reduce of the packed blocks", "none": "single GPU"}[exchange],
         "edges_this_rank": ne, "dim": sg.plan.dim,
         "accumulate_ms": round(acc_ms, 4), "solve_update_ms": round(ms - acc_ms, 4),
+        "solve_path": {0: "steps (one launch per block step)", 1: "fused (persistent chain + workers)",
+                       2: "tiles (dataflow over shared-memory-resident tiles)"}[solve_path],
         "precision": precision, "_poses": poses_after.cpu(),
         "roofline": {"bound": "hbm",
                      "kernel": "gn_accum_stream_kernel" if precision == "mixed" else "gn_accum_kernel",

@@ -227,6 +227,10 @@ void m3s_gn_plan_destroy(m3s_gn_plan* plan);
 int m3s_gn_plan_num_free(const m3s_gn_plan* plan);      /* F; 0 => solver is a no-op (early out) */
 int m3s_gn_plan_dim(const m3s_gn_plan* plan);           /* 7 F */
 int m3s_gn_plan_ld(const m3s_gn_plan* plan);            /* row stride of H: dim rounded up to 32 */
+/* factorisation path m3s_gn_solve_update will take for this plan on the current device:
+ * 0 = one launch per block step, 1 = persistent chain + workers (M3S_GN_CHOL=fused),
+ * 2 = dataflow over shared-memory-resident tiles (default when every tile CTA is co-resident) */
+int m3s_gn_plan_factor_path(m3s_gn_plan* plan);
 /* device pointer + element count of the packed per-edge blocks [E][M3S_GN_EDGE_STRIDE] f64 that
  * m3s_gn_accumulate writes and m3s_gn_solve_update reads: the buffer a multi-GPU caller
  * all-reduces (sum) between the two when edges are sharded across ranks. */

@@ -1973,6 +1973,591 @@ chol_fused_kernel(Status* __restrict__ status, double* Hm, double* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Dataflow factorisation (default when every tile CTA is co-resident; M3S_GN_CHOL=steps|fused select the
+// other paths): ONE cooperative launch in which every 64x64 tile of the lower triangle stays in the shared
+// memory of the CTA that owns it for the whole factorisation; the only global traffic per block step
+// is the 32-column panel and the only synchronisation are per-panel acquire/release flags (no grid
+// barrier, no kernel boundary):
+//   * 64x64 tiles (r, c), 32-column block steps k (tile column c holds steps 2c and 2c + 1).
+//   * the factor is kept as M_k = G_kk^-1 with M_k A_kk M_k^T = I (ANY such M works: the panel is
+//     P_rk = A_rk M_k^T, the trailing update A_rc -= P_rk P_ck^T, the right-hand-side row is one more
+//     panel row, and the back-substitution needs G_kk^-T = M_k^T): the triangular solves of the step
+//     kernels become 32^3 GEMMs and the Cholesky factor of the diagonal block is never formed.
+//   * tl_elim32_w: M_k by a block LDL^T with 2x2 pivots on three warps (see there).
+//   * roles: CTA d < nt owns the diagonal tile (d, d) and the 64 right-hand-side entries of tile column
+//     d; every tile (r, c), r > c, has a CTA of its own.  The chain from one diagonal tile to the next:
+//     M_{2d+1} -> [tile (d+1, d): panel = S M^T, publish] -> [CTA d+1: T -= P P^T, two eliminations].
+//     The diagonal CTAs and the tiles (c + 1, c) take the blocks that are dispatched to SMs without a
+//     second CTA (cooperative launch, 253 CTAs for 22 tile rows on 148 SMs, 2 CTAs per SM at most).
+// Flags are monotonic words zeroed by a memset before the launch; a wait is one thread per flag polling
+// with ld.acquire (bounded: a lost producer turns into status->failed and an abort word that releases
+// every other wait); data written during the launch is read with ld.global.cg.
+// MEASURED (B200, 200 keyframes = 44 block steps, scripts/gn_solve_timeline.py, profiles/r2_gn_timeline_*):
+// factorisation 457 us (launch-per-step path: 495 us); per diagonal tile ~20.8 us = elimination 3.3 +
+// [M stored, P10, T11 update, fence, publish] 2.9 + elimination 3.7 + publish 0.4 + [tile (d+1, d): hop,
+// panel GEMM, store, fence, publish; CTA d+1: hop] 6 + panel load 1.2 + T update 2.3.  What the numbers
+// say about this GPU (profiles/microbench/latency_b200.txt): dependent DFMA 8.7 clk but only ~53 DFMA
+// lanes/clk/SM, L2 round trip ~300 clk, __threadfence ~410 clk, st.release.gpu ~790 clk -- a flag hop with
+// its data costs ~1.5 us, and a 64x64x32 update ~1.3 us of a whole SM.
+// ------------------------------------------------------------------------------------------------
+constexpr int kTS = 64;          // tile size
+constexpr int kTlThreads = 256;
+constexpr int kTP = 66;          // tile pitch in doubles (16-B aligned rows, conflict-free column walks)
+constexpr int kPP = 34;          // panel pitch in doubles
+
+struct TilesSmem {
+    double T[kTS][kTP];    // diagonal tile (d, d)                       (diagonal CTAs)
+    double S[kTS][kTP];    // tile (d, d-1) / the off-diagonal CTA's tile
+    double PA[kTS][kPP];   // panel rows of this tile row; scratch of elim32
+    double PB[kTS][kPP];   // panel rows of the tile column
+    double Mi[kNB][kPP];   // M_k
+    double rhs[kTS];       // right-hand-side entries of tile column d
+    double yk[kNB];
+    double piv[16][4];     // elim32: (alpha, beta, det) of each 2x2 pivot
+    int wres[2][4];        // results of the flag waits (double-buffered: one barrier per wait)
+    int prog;              // elim32: pivots published by warp 0
+    int hsflag;            // elim32: segments handed over by warp 2
+    int bad;
+};
+
+// control words: [0] abort | lflag[2 nt] | p10flag[nt] | yflag[2 nt] | pflag[2 nt][nt]
+__host__ __device__ inline int tl_ctl_words(int nt) { return 8 + 5 * nt + 2 * nt * nt; }
+struct TilesCtl {
+    unsigned* abort_w;
+    unsigned* lflag;
+    unsigned* p10flag;
+    unsigned* yflag;
+    unsigned* pflag;
+    int nt;
+    __device__ TilesCtl(unsigned* ctl, int nt_) : abort_w(ctl), lflag(ctl + 8), p10flag(ctl + 8 + 2 * nt_),
+                                                   yflag(ctl + 8 + 3 * nt_), pflag(ctl + 8 + 5 * nt_), nt(nt_) {}
+    __device__ unsigned* panel(int k, int r) const { return pflag + k * nt + r; }
+};
+
+// Wait for up to three flags (null = none): lane 0 of warps 0..2 poll one each.  One barrier per call.
+__device__ __forceinline__ bool tl_wait(TilesSmem& sm, int& phase, const TilesCtl& ctl, const unsigned* f0,
+                                        const unsigned* f1, const unsigned* f2) {
+    const int tid = threadIdx.x;
+    const int slot = phase & 1;
+    phase ^= 1;
+    if ((tid & 31) == 0 && tid < 96) {
+        const unsigned* f = (tid == 0) ? f0 : (tid == 32 ? f1 : f2);
+        int ok = 1;
+        if (f != nullptr) {
+            int spins = 0;
+            while (ld_acquire_u32(f) == 0u) {
+                ++spins;
+                if (spins > kGridSpinLimit || ((spins & 63) == 0 && ld_acquire_u32(ctl.abort_w) != 0u)) { ok = 0; break; }
+            }
+            if (!ok) st_release_u32(ctl.abort_w, 1u);
+        }
+        sm.wres[slot][tid >> 5] = ok;
+    }
+    __syncthreads();
+    return (sm.wres[slot][0] & sm.wres[slot][1] & sm.wres[slot][2]) != 0;
+}
+
+// after the data stores of all threads and a __syncthreads: one thread publishes
+__device__ __forceinline__ void st_relaxed_u32(unsigned* p, unsigned v) {
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void tl_publish(unsigned* flag) {
+    __threadfence();
+    st_relaxed_u32(flag, 1u);
+}
+
+// 64x64 tile of the assembled matrix (rows r0.., columns c0..); beyond np: identity
+__device__ __forceinline__ void tl_load_tile(double (*dst)[kTP], const double* __restrict__ Hm, int np, int r0, int c0) {
+    for (int i = threadIdx.x; i < kTS * kTS / 2; i += kTlThreads) {
+        const int r = i >> 5, c = (i & 31) * 2;
+        const int gr = r0 + r, gc = c0 + c;
+        double2 v;
+        if (gr < np && gc + 1 < np) v = *reinterpret_cast<const double2*>(Hm + (size_t)gr * np + gc);
+        else {
+            v.x = (gr < np && gc < np) ? Hm[(size_t)gr * np + gc] : ((gr == gc) ? 1.0 : 0.0);
+            v.y = (gr < np && gc + 1 < np) ? Hm[(size_t)gr * np + gc + 1] : ((gr == gc + 1) ? 1.0 : 0.0);
+        }
+        *reinterpret_cast<double2*>(&dst[r][c]) = v;
+    }
+}
+
+// `rows` panel rows (r0.., columns 32 k ..) of the factor written during this launch; rows >= np: 0
+__device__ __forceinline__ void tl_load_panel(double (*dst)[kPP], const double* Lm, int np, int r0, int k, int rows) {
+    for (int i = threadIdx.x; i < rows * (kNB / 2); i += kTlThreads) {
+        const int r = i >> 4, c = (i & 15) * 2;
+        double2 v = make_double2(0.0, 0.0);
+        if (r0 + r < np) v = __ldcg(reinterpret_cast<const double2*>(Lm + (size_t)(r0 + r) * np + k * kNB + c));
+        *reinterpret_cast<double2*>(&dst[r][c]) = v;
+    }
+}
+__device__ __forceinline__ void tl_store_panel(const double (*src)[kPP], double* Lm, int np, int r0, int k, int rows) {
+    for (int i = threadIdx.x; i < rows * (kNB / 2); i += kTlThreads) {
+        const int r = i >> 4, c = (i & 15) * 2;
+        if (r0 + r < np)
+            *reinterpret_cast<double2*>(Lm + (size_t)(r0 + r) * np + k * kNB + c) = *reinterpret_cast<const double2*>(&src[r][c]);
+    }
+}
+__device__ __forceinline__ void tl_load_block32(double (*dst)[kPP], const double* src) {  // Linv block, row-major 32x32
+    for (int i = threadIdx.x; i < kNB * kNB / 2; i += kTlThreads) {
+        const int r = i >> 4, c = (i & 15) * 2;
+        *reinterpret_cast<double2*>(&dst[r][c]) = __ldcg(reinterpret_cast<const double2*>(src + r * kNB + c));
+    }
+}
+__device__ __forceinline__ void tl_store_block32(const double (*src)[kPP], double* dst) {
+    for (int i = threadIdx.x; i < kNB * kNB / 2; i += kTlThreads) {
+        const int r = i >> 4, c = (i & 15) * 2;
+        *reinterpret_cast<double2*>(dst + r * kNB + c) = *reinterpret_cast<const double2*>(&src[r][c]);
+    }
+}
+
+// acc[i][j] = sum_k A[ty + 16 i][k] B[tx + 16 j][k], k < 32 (thread grid 16 x 16; lda, ldb even)
+template <int MI, int NJ>
+__device__ __forceinline__ void tl_gemm_nt(const double* A, int lda, const double* B, int ldb, double (&acc)[MI][NJ]) {
+    const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) acc[i][j] = 0.0;
+#pragma unroll 4
+    for (int k = 0; k < kNB; k += 2) {
+        double2 a[MI], b[NJ];
+#pragma unroll
+        for (int i = 0; i < MI; ++i) a[i] = *reinterpret_cast<const double2*>(A + (ty + 16 * i) * lda + k);
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) b[j] = *reinterpret_cast<const double2*>(B + (tx + 16 * j) * ldb + k);
+#pragma unroll
+        for (int i = 0; i < MI; ++i)
+#pragma unroll
+            for (int j = 0; j < NJ; ++j) acc[i][j] = fma(a[i].y, b[j].y, fma(a[i].x, b[j].x, acc[i][j]));
+    }
+}
+template <int MI, int NJ>
+__device__ __forceinline__ void tl_sub(double* Cm, int ldc, const double (&acc)[MI][NJ]) {
+    const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) Cm[(ty + 16 * i) * ldc + tx + 16 * j] -= acc[i][j];
+}
+template <int MI, int NJ>
+__device__ __forceinline__ void tl_put(double* Cm, int ldc, const double (&acc)[MI][NJ]) {
+    const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) Cm[(ty + 16 * i) * ldc + tx + 16 * j] = acc[i][j];
+}
+
+// out[i] (+)= sign * sum_m v[m] P[i][m], i < rows (4 threads per output)
+__device__ __forceinline__ void tl_rowdot(const double (*P)[kPP], const double* v, double* out, int rows, bool subtract) {
+    const int i = threadIdx.x >> 2, part = threadIdx.x & 3;
+    double s = 0.0;
+    if (i < rows) {
+#pragma unroll
+        for (int m = 0; m < 8; ++m) s = fma(v[part * 8 + m], P[i][part * 8 + m], s);
+    }
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    if (i < rows && part == 0) out[i] = subtract ? out[i] - s : s;
+}
+
+// M (32 x 32, into Mo) with M W M^T = I for the symmetric block W = Tm[o .. o+31][o .. o+31]: block LDL^T
+// with 2x2 pivots, W = L D L^T, M = D^-1/2 L^-1 (the dependent chain per PAIR of columns is
+// det = a c - b^2 -> ONE reciprocal -> one FMA per updated entry, instead of shuffle -> rsqrt -> scale ->
+// update per column).  Called by three warps (kElimWarp0 .. +2; no block barrier inside; sm.prog =
+// sm.hsflag = 0 and a block barrier before the call, a block barrier after it):
+//   chain   the dependent chain, 8 columns (one SEGMENT) in registers at a time; publishes the pivot
+//           columns X, Y, the multipliers M1, M2 and the pivots of every pair through shared memory;
+//   inverse N = L^-1 and M = D^-1/2 N from the published multipliers (lane = column, registers);
+//   helper  owns the columns of the segments the chain has not reached yet, applies every published pair
+//           to them and hands a segment over through `hs` two pairs before the chain needs it.
+// What shaped this code (clock stamps per pair via `dbg`, profiles/microbench/elim_bench.cu):
+//   * with all 32 columns in the chain warp's registers ptxas scheduled ~60 trailing DFMAs in front of
+//     each determinant (in-order issue: 450 clk per pair) -> trailing update on the helper warp;
+//   * run by warps 0-2 of the factorisation kernel -- the warps whose lane 0 polls the flags, writes the
+//     time stamps and does the other single-thread jobs -- every warp-synchronising instruction of the
+//     chain (SHFL.IDX, then __syncwarp) took 200-700 clk for the first pairs of each call: 17 400 clk
+//     per elimination against 6 200 on warps 4-6 (same code, same data; stand-alone: 6 200 on any warp).
+//     Hence kElimWarp0 = 4 and shared-memory broadcasts instead of shuffles;
+//   * GEMM work of other warps of the same CTA beside the elimination (tried: 128 workers doing the
+//     T10 / T11 updates meanwhile) slows the chain 5x through the shared-memory pipeline -> the
+//     elimination runs alone on its SM.
+// sc = 4 x 16 x 32 doubles (X, Y, M1, M2), hs = 8 x 32 doubles.  ~6 500 clk = 3.4 us per call.
+#ifdef M3S_TL_SPIN_SLEEP
+#define TL_SPIN_PAUSE __nanosleep(M3S_TL_SPIN_SLEEP);
+#else
+#define TL_SPIN_PAUSE
+#endif
+#if defined(M3S_TL_NOFENCE)
+#define TL_FENCE_BLOCK
+#elif defined(M3S_TL_ACQREL)
+#define TL_FENCE_BLOCK asm volatile("fence.acq_rel.cta;" ::: "memory");
+#else
+#define TL_FENCE_BLOCK __threadfence_block();
+#endif
+// the three elimination warps: NOT warp 0 (thread 0 polls flags, writes time stamps and carries other
+// single-thread duties; see the measurements in DESIGN.md)
+#ifndef M3S_TL_ELIM_WARP0
+#define M3S_TL_ELIM_WARP0 4
+#endif
+constexpr int kElimWarp0 = M3S_TL_ELIM_WARP0;
+__device__ __forceinline__ bool tl_is_elim_warp() {
+    const int w = (int)(threadIdx.x >> 5) - kElimWarp0;
+    return w >= 0 && w <= 2;
+}
+__device__ __noinline__ void tl_elim32_w(TilesSmem& sm, double (*Tm)[kTP], int o, double* sc, double* hs,
+                                         double (*Mo)[kPP], long long* dbg) {
+    const int lane = threadIdx.x & 31, warp = (int)(threadIdx.x >> 5) - kElimWarp0;
+    double* X = sc;
+    double* Y = sc + 512;
+    double* M1 = sc + 1024;
+    double* M2 = sc + 1536;
+    volatile int* prog = &sm.prog;
+    volatile int* hsf = &sm.hsflag;
+    if (dbg != nullptr && warp == 0 && lane == 0) dbg[48] = clock64();
+    if (warp == 0) {
+        // a[]: the 8 columns of the current segment; b[]: the next segment's, received from warp 2 TWO pairs
+        // before the chain gets there (the hand-over latency, ~400 clk, hides behind pairs 2 and 3, whose
+        // updates of those columns the chain then applies itself)
+        double a[8], b[8];
+        bool isbad = false;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) { a[c] = Tm[o + c][o + lane]; b[c] = 0.0; }   // W[lane][c] by symmetry: conflict-free
+#pragma unroll 1
+        for (int s = 0; s < 4; ++s) {
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                const int q = 4 * s + p, j = 2 * q;
+                if (p == 2 && s < 3) {
+                    while (*hsf < s + 1) { TL_SPIN_PAUSE }
+                    __syncwarp();
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) b[c] = hs[c * 32 + lane];
+                }
+                // The pivot block and the pivot-column entries of the rows that follow go through SHARED
+                // MEMORY (store own x, y -> __syncwarp -> broadcast loads), not through shuffles (30 SHFL per
+                // pair cost more issue slots and, measured inside the factorisation kernel, far more time).
+                const double x = a[2 * p], y = a[2 * p + 1];
+                X[q * 32 + lane] = x;
+                Y[q * 32 + lane] = y;
+                __syncwarp();
+                double al = X[q * 32 + j];
+                double be = X[q * 32 + j + 1];
+                double ga = Y[q * 32 + j + 1];
+                double xc[8], yc[8], xn[8], yn[8];
+#pragma unroll
+                for (int c = 2 * p + 2; c < 8; c += 2) {
+                    const double2 xv = *reinterpret_cast<const double2*>(X + q * 32 + 8 * s + c);
+                    const double2 yv = *reinterpret_cast<const double2*>(Y + q * 32 + 8 * s + c);
+                    xc[c] = xv.x; xc[c + 1] = xv.y;
+                    yc[c] = yv.x; yc[c + 1] = yv.y;
+                }
+                if (p >= 2 && s < 3) {
+#pragma unroll
+                    for (int c = 0; c < 8; c += 2) {
+                        const double2 xv = *reinterpret_cast<const double2*>(X + q * 32 + 8 * s + 8 + c);
+                        const double2 yv = *reinterpret_cast<const double2*>(Y + q * 32 + 8 * s + 8 + c);
+                        xn[c] = xv.x; xn[c + 1] = xv.y;
+                        yn[c] = yv.x; yn[c + 1] = yv.y;
+                    }
+                }
+                double det = fma(al, ga, -(be * be));
+                if (!(al > 1e-290) || !(det > 1e-300) || !(det < 1e300)) {  // warp-uniform
+                    isbad = true;
+                    al = 1.0; be = 0.0; ga = 1.0; det = 1.0;
+                }
+                const double r = rcp_fast(det);
+                const double n1 = fma(x, ga, -(y * be)), n2 = fma(y, al, -(x * be));   // independent of r
+#pragma unroll
+                for (int c = 2 * p + 2; c < 8; ++c) {
+                    const double z = fma(n1, xc[c], n2 * yc[c]);                        // independent of r
+                    a[c] = fma(-r, z, a[c]);                                            // ONE op after the reciprocal
+                }
+                if (p >= 2 && s < 3) {
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        const double z = fma(n1, xn[c], n2 * yn[c]);
+                        b[c] = fma(-r, z, b[c]);
+                    }
+                }
+                M1[q * 32 + lane] = n1 * r;
+                M2[q * 32 + lane] = n2 * r;
+                if (lane == 0) { sm.piv[q][0] = al; sm.piv[q][1] = be; sm.piv[q][2] = det; }
+                __syncwarp();
+                if (lane == 0) { TL_FENCE_BLOCK *prog = q + 1; if (dbg != nullptr) dbg[q] = clock64(); }
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c) a[c] = b[c];
+        }
+        if (isbad && lane == 0) sm.bad = 1;
+    } else if (warp == 1) {
+        // lane = column c of N in registers (loop over the pairs fully unrolled: static register indices)
+        double n[kNB];
+#pragma unroll
+        for (int i = 0; i < kNB; ++i) n[i] = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+        for (int q = 0; q < 16; ++q) {
+            const int j = 2 * q;
+            while (*prog < q + 1) { TL_SPIN_PAUSE }
+            __syncwarp();
+            const double nj = n[j], nj1 = n[j + 1];
+            const double2* m1v = reinterpret_cast<const double2*>(M1 + q * 32);
+            const double2* m2v = reinterpret_cast<const double2*>(M2 + q * 32);
+#pragma unroll
+            for (int i = j + 2; i < kNB; i += 2) {
+                const double2 u = m1v[i >> 1], v = m2v[i >> 1];
+                n[i] = fma(-v.x, nj1, fma(-u.x, nj, n[i]));
+                n[i + 1] = fma(-v.y, nj1, fma(-u.y, nj, n[i + 1]));
+            }
+            const double al = sm.piv[q][0], be = sm.piv[q][1], det = sm.piv[q][2];
+            // F with F D F^T = I for D = [[al, be], [be, ga]]: F = [[1/sqrt(al), 0], [-be / (al s), 1/s]], s^2 = det / al
+            const double ra = rsqrt_fast(al);
+            const double ia = ra * ra;
+            const double rs = rsqrt_fast(det * ia);
+            const double f10 = -(be * ia) * rs;
+            Mo[j][lane] = ra * nj;
+            Mo[j + 1][lane] = fma(f10, nj, rs * nj1);
+            if (dbg != nullptr && lane == 0) dbg[16 + q] = clock64();
+        }
+    } else if (warp == 2) {
+        double h[24];   // columns 8 .. 31 of row `lane`
+#pragma unroll
+        for (int c = 0; c < 24; ++c) h[c] = Tm[o + 8 + c][o + lane];
+        // Loop over the pairs fully unrolled (static register indices).  Segment sg + 1 is handed over after
+        // pair 4 sg + 1 -- two pairs before the chain needs it; the chain applies pairs 4 sg + 2, 4 sg + 3 to
+        // it itself -- and those 8 columns are updated and published first, the rest afterwards.
+#pragma unroll
+        for (int q = 0; q < 10; ++q) {
+            while (*prog < q + 1) { TL_SPIN_PAUSE }
+            __syncwarp();
+            const double m1 = M1[q * 32 + lane], m2 = M2[q * 32 + lane];
+            const double2* Xq = reinterpret_cast<const double2*>(X + q * 32);
+            const double2* Yq = reinterpret_cast<const double2*>(Y + q * 32);
+            const int sg = q / 4;
+            // first column still owned here: segment sg + 1 until it is handed over (after q % 4 == 1)
+            const int c0 = ((q & 3) <= 1) ? 8 * (sg + 1) : 8 * (sg + 2);
+#pragma unroll
+            for (int c = c0; c < c0 + 8 && c < kNB; c += 2) {
+                const double2 xv = Xq[c >> 1], yv = Yq[c >> 1];
+                h[c - 8] = fma(-m2, yv.x, fma(-m1, xv.x, h[c - 8]));
+                h[c - 7] = fma(-m2, yv.y, fma(-m1, xv.y, h[c - 7]));
+            }
+            if ((q & 3) == 1) {
+#pragma unroll
+                for (int c = 0; c < 8; ++c) hs[c * 32 + lane] = h[c0 - 8 + c];
+                __syncwarp();
+                if (lane == 0) { TL_FENCE_BLOCK *hsf = sg + 1; }
+            }
+#pragma unroll
+            for (int c = c0 + 8; c < kNB; c += 2) {
+                const double2 xv = Xq[c >> 1], yv = Yq[c >> 1];
+                h[c - 8] = fma(-m2, yv.x, fma(-m1, xv.x, h[c - 8]));
+                h[c - 7] = fma(-m2, yv.y, fma(-m1, xv.y, h[c - 7]));
+            }
+            if (dbg != nullptr && lane == 0) dbg[32 + q] = clock64();
+        }
+    }
+}
+
+// block-wide wrapper (all 256 threads): nothing runs beside the elimination
+__device__ __forceinline__ void tl_elim32(TilesSmem& sm, double (*Tm)[kTP], int o, double* sc, double* hs,
+                                          double (*Mo)[kPP]) {
+    if (threadIdx.x == 0) { sm.prog = 0; sm.hsflag = 0; }
+    __syncthreads();
+    if (tl_is_elim_warp()) tl_elim32_w(sm, Tm, o, sc, hs, Mo, nullptr);
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(kTlThreads, 2)
+chol_tiles_kernel(Status* __restrict__ status, const double* __restrict__ Hm, double* Lm, double* Linv, int np,
+                  unsigned* ctlw, int first_diag, long long* __restrict__ tl) {
+    if (status->stopped | status->failed) return;   // uniform over the grid (written by earlier kernels only)
+    extern __shared__ __align__(16) unsigned char tl_smem_raw[];
+    TilesSmem& sm = *reinterpret_cast<TilesSmem*>(tl_smem_raw);
+    const int tid = threadIdx.x;
+    const int nblk = np / kNB;
+    const int nt = (np + kTS - 1) / kTS;
+    const TilesCtl ctl(ctlw, nt);
+    int phase = 0;
+    if (tid == 0) sm.bad = 0;
+    const double* ybase = Lm + (size_t)np * np;   // row np of the factor: y
+    double* ystore = Lm + (size_t)np * np;
+
+    // Role of this CTA.  CTAs are dispatched breadth-first (block b < #SMs -> SM b, the rest fill the
+    // second slot of SMs 0, 1, ...): the nt diagonal CTAs -- the dependent chain -- take the LAST nt
+    // blocks of the first wave (first_diag = min(#SMs, grid) - nt), whose SMs get no second CTA as long as
+    // grid <= 2 #SMs - nt, so no neighbour competes for their fp64 pipe.  Correct for any dispatch order.
+    const int bid = (int)blockIdx.x;
+    const bool is_diag = bid >= first_diag && bid < first_diag + nt;
+    if (tid == 0 && tl != nullptr && bid < 232) {   // placement diagnostics (scripts/gn_solve_timeline.py)
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        tl[16 * nblk + 120 + bid] = (long long)smid + 1;
+    }
+    if (is_diag) {
+        // ------------------------------ diagonal CTA d ------------------------------------------
+        const int d = bid - first_diag;
+        if (tid == 0 && tl != nullptr) {
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            tl[16 * nblk + d] = (long long)smid;   // who = 1 phase slots are unused by this kernel
+        }
+        const int r0 = d * kTS;
+        tl_load_tile(sm.T, Hm, np, r0, r0);
+        if (tid < kTS) sm.rhs[tid] = (r0 + tid < np) ? Hm[(size_t)np * np + r0 + tid] : 0.0;
+        __syncthreads();
+        // Scratch of the eliminations: S rows 0 .. 31 (this CTA has no second tile) = elim32's X / Y / M1 /
+        // M2, PB rows 0 .. 31 = the segment hand-over buffer, PB rows 32 .. 63 = a second M buffer.
+        double* esc = &sm.S[0][0];
+        double* ehs = &sm.PB[0][0];
+        double (*MiB)[kPP] = reinterpret_cast<double (*)[kPP]>(&sm.PB[kNB][0]);
+        // block steps 0 .. 2d-1: the panels of tile row d (the last two come from tile (d, d-1), one flag hop
+        // after M_{2d-2} / M_{2d-1}: that hop + this update is what separates two diagonal tiles on the chain)
+        for (int k = 0; k < 2 * d; ++k) {
+            const bool last = (k == 2 * d - 1);
+            if (last && tid == 0) tl_stamp(tl, 8 * nblk + 8 * k + 3);
+            if (!tl_wait(sm, phase, ctl, ctl.panel(k, d), ctl.yflag + k, nullptr)) goto lost;
+            if (last && tid == 0) tl_stamp(tl, 8 * nblk + 8 * k + 4);
+            tl_load_panel(sm.PA, Lm, np, r0, k, kTS);
+            if (tid < kNB) sm.yk[tid] = __ldcg(ybase + k * kNB + tid);
+            __syncthreads();
+            if (last && tid == 0) tl_stamp(tl, 8 * nblk + 8 * k + 5);
+            {
+                double acc[4][4];
+                tl_gemm_nt<4, 4>(&sm.PA[0][0], kPP, &sm.PA[0][0], kPP, acc);
+                tl_sub<4, 4>(&sm.T[0][0], kTP, acc);
+            }
+            tl_rowdot(sm.PA, sm.yk, sm.rhs, kTS, true);
+            __syncthreads();
+            if (last && tid == 0) tl_stamp(tl, 8 * nblk + 8 * k + 6);
+        }
+        // ---- block step 2d: first elimination
+        if (tid == 0) { sm.prog = 0; sm.hsflag = 0; tl_stamp(tl, (0 * nblk + 2 * d) * 2); }
+        __syncthreads();
+        if (tl_is_elim_warp()) tl_elim32_w(sm, sm.T, 0, esc, ehs, MiB, (tl != nullptr && d == 3) ? tl + 16 * nblk + 64 : nullptr);
+        __syncthreads();
+        // ---- block step 2d: M_{2d} is in MiB
+        {
+            const int k = 2 * d;
+            if (tid == 0) tl_stamp(tl, 8 * nblk + 8 * k + 0);
+            tl_store_block32(MiB, Linv + (size_t)k * kNB * kNB);
+            tl_rowdot(MiB, sm.rhs, sm.yk, kNB, false);                     // y_k = M_k rhs_k
+            const bool second = k + 1 < nblk;
+            if (second) {
+                double acc[2][2];
+                tl_gemm_nt<2, 2>(&sm.T[kNB][0], kTP, &MiB[0][0], kPP, acc);   // P10 = T10 M^T
+                tl_put<2, 2>(&sm.PA[0][0], kPP, acc);
+            }
+            __syncthreads();
+            if (tid < kNB) ystore[k * kNB + tid] = sm.yk[tid];
+            if (second) {
+                tl_store_panel(sm.PA, Lm, np, r0 + kNB, k, kNB);
+                double acc[2][2];
+                tl_gemm_nt<2, 2>(&sm.PA[0][0], kPP, &sm.PA[0][0], kPP, acc);
+                tl_sub<2, 2>(&sm.T[kNB][kNB], kTP, acc);
+                tl_rowdot(sm.PA, sm.yk, sm.rhs + kNB, kNB, true);
+            }
+            if (tid == 0) { sm.prog = 0; sm.hsflag = 0; }
+            __syncthreads();
+            if (tid == 96) {   // ONE fence for everything stored since the last publish, finished BEFORE the chain goes on
+                __threadfence();
+                st_relaxed_u32(ctl.lflag + k, 1u);
+                st_relaxed_u32(ctl.yflag + k, 1u);
+                st_relaxed_u32(ctl.p10flag + d, 1u);
+            }
+#ifdef M3S_TL_SYNC_PUBLISH   // A/B: finish the fence before the second elimination starts
+            __syncthreads();
+#endif
+            if (tid == 0) tl_stamp(tl, (0 * nblk + k) * 2 + 1);
+            if (second) {
+                // ---- block step 2d+1
+                if (tid == 0) tl_stamp(tl, (0 * nblk + k + 1) * 2);
+                if (tl_is_elim_warp()) tl_elim32_w(sm, sm.T, kNB, esc, ehs, sm.Mi, nullptr);
+                __syncthreads();
+                if (tid == 0) tl_stamp(tl, 8 * nblk + 8 * (k + 1) + 0);
+                tl_store_block32(sm.Mi, Linv + (size_t)(k + 1) * kNB * kNB);
+                tl_rowdot(sm.Mi, sm.rhs + kNB, sm.yk, kNB, false);
+                __syncthreads();
+                if (tid < kNB) ystore[(k + 1) * kNB + tid] = sm.yk[tid];
+                __syncthreads();
+                if (tid == 0) tl_stamp(tl, (0 * nblk + k + 1) * 2 + 1);
+                if (tid == 64) {
+                    __threadfence();
+                    st_relaxed_u32(ctl.lflag + k + 1, 1u);
+                    st_relaxed_u32(ctl.yflag + k + 1, 1u);
+                }
+            }
+        }
+        if (sm.bad && tid == 0) status->chol_fail = 1;
+        return;
+    }
+    {
+        // ------------------------------ off-diagonal CTA (r, c), r > c ---------------------------
+        int t = bid < first_diag ? bid : bid - nt, c = 0;
+        // Enumeration: the R = min(nt - 1, first_diag) blocks right before the diagonal CTAs take the tiles
+        // (c + 1, c) -- each one flag hop inside the chain -- so that they, too, land on SMs without a
+        // second CTA; every other block takes the remaining tiles in column order.
+        int r;
+        {
+            const int R = min(nt - 1, first_diag), sub0 = first_diag - R;
+            if (t >= sub0 && t < first_diag) {
+                c = t - sub0;
+                r = c + 1;
+            } else {
+                int u = t < sub0 ? t : t - R;
+                if (u < nt - 1 - R) {          // sub-diagonal tiles that found no reserved block
+                    c = R + u;
+                    r = c + 1;
+                } else {
+                    u -= nt - 1 - R;
+                    c = 0;
+                    while (u >= nt - 2 - c) { u -= nt - 2 - c; ++c; }
+                    r = c + 2 + u;
+                }
+            }
+        }
+        const int r0 = r * kTS, c0 = c * kTS;
+        tl_load_tile(sm.S, Hm, np, r0, c0);
+        __syncthreads();
+        for (int k = 0; k < 2 * c; ++k) {
+            if (!tl_wait(sm, phase, ctl, ctl.panel(k, r), ctl.panel(k, c), nullptr)) goto lost;
+            tl_load_panel(sm.PA, Lm, np, r0, k, kTS);
+            tl_load_panel(sm.PB, Lm, np, c0, k, kTS);
+            __syncthreads();
+            double acc[4][4];
+            tl_gemm_nt<4, 4>(&sm.PA[0][0], kPP, &sm.PB[0][0], kPP, acc);
+            tl_sub<4, 4>(&sm.S[0][0], kTP, acc);
+            __syncthreads();
+        }
+        for (int h = 0; h < 2; ++h) {
+            const int k = 2 * c + h;
+            if (!tl_wait(sm, phase, ctl, ctl.lflag + k, h == 0 ? ctl.p10flag + c : nullptr, nullptr)) goto lost;
+            tl_load_block32(sm.Mi, Linv + (size_t)k * kNB * kNB);
+            if (h == 0) tl_load_panel(sm.PB, Lm, np, c0 + kNB, k, kNB);
+            __syncthreads();
+            {
+                double acc[4][2];
+                tl_gemm_nt<4, 2>(&sm.S[0][kNB * h], kTP, &sm.Mi[0][0], kPP, acc);
+                tl_put<4, 2>(&sm.PA[0][0], kPP, acc);
+            }
+            __syncthreads();
+            tl_store_panel(sm.PA, Lm, np, r0, k, kTS);
+            if (h == 0) {
+                double acc[4][2];
+                tl_gemm_nt<4, 2>(&sm.PA[0][0], kPP, &sm.PB[0][0], kPP, acc);
+                tl_sub<4, 2>(&sm.S[0][kNB], kTP, acc);
+            }
+            __syncthreads();
+            if (tid == 64) tl_publish(ctl.panel(k, r));
+        }
+        return;
+    }
+lost:
+    // a producer did not publish within the bound (or another CTA aborted): never hang the device
+    if (tid == 0) status->failed = 1;
+}
+
+// ------------------------------------------------------------------------------------------------
 // Back-substitution L^T dx = y (y = rhs row of the factorised augmented matrix), ||dx|| test
 // (gauss_newton.py:263-265: stop BEFORE applying) and Sim3 retraction (sim3_ops.py:129-251) in one
 // kernel.
@@ -2243,6 +2828,8 @@ struct m3s_gn_plan {
     int* flags = nullptr;           // [np / 32] publication flags of the back-substitution
     unsigned* gbar = nullptr;       // grid-barrier counter of the persistent factorisation
     int fused_grid = -1;            // CTAs of chol_fused_kernel (0 = not available, -1 = not probed)
+    unsigned* tctl = nullptr;       // flag words of the dataflow factorisation (chol_tiles_kernel)
+    int tiles_grid = -1;            // its CTA count (0 = not available / not selected, -1 = not probed)
     long long* timeline = nullptr;  // [4, np / 32, 2] globaltimer stamps (M3S_GN_TIMELINE=1), else null
     double* g = nullptr;            // [dim]
     double* dx = nullptr;           // [dim]
@@ -2295,7 +2882,7 @@ static void plan_free(m3s_gn_plan* p) {
     xch_free(p);
     if (p->graph_exec) cudaGraphExecDestroy(p->graph_exec);
     if (p->graph) cudaGraphDestroy(p->graph);
-    cudaFree(p->Lm); cudaFree(p->xsol); cudaFree(p->flags); cudaFree(p->gbar); cudaFree(p->timeline);
+    cudaFree(p->Lm); cudaFree(p->xsol); cudaFree(p->flags); cudaFree(p->gbar); cudaFree(p->tctl); cudaFree(p->timeline);
     cudaFree(p->poses); cudaFree(p->meta); cudaFree(p->partials); cudaFree(p->edge_blocks);
     cudaFree(p->blocks); cudaFree(p->list_edge); cudaFree(p->list_sign); cudaFree(p->free_kf);
     cudaFree(p->Hm); cudaFree(p->Ldiag); cudaFree(p->Linv); cudaFree(p->g); cudaFree(p->dx); cudaFree(p->status);
@@ -2432,6 +3019,7 @@ M3S_API m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii, const int32_t* jj, in
     ok = ok && cudaMalloc((void**)&p->xsol, sizeof(double) * std::max(p->np, kNB)) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&p->flags, sizeof(int) * nblk) == cudaSuccess;
     ok = ok && cudaMalloc((void**)&p->gbar, 64) == cudaSuccess;
+    ok = ok && cudaMalloc((void**)&p->tctl, sizeof(unsigned) * tl_ctl_words((p->np + kTS - 1) / kTS)) == cudaSuccess;
     if (const char* tlv = getenv("M3S_GN_TIMELINE")) {
         if (tlv[0] == '1') {
             ok = ok && cudaMalloc((void**)&p->timeline, sizeof(long long) * 24 * nblk) == cudaSuccess &&
@@ -2763,12 +3351,49 @@ static int fused_grid_size(m3s_gn_plan* plan) {
     return plan->fused_grid;
 }
 
-// assemble + blocked Cholesky of the augmented matrix, enqueued on `st`: one cooperative launch
-// (chol_fused_kernel) or, as the fallback, one launch per block step
+// Grid of the dataflow factorisation (chol_tiles_kernel): one CTA per diagonal tile + one per tile
+// (r, c) with r - c >= 2; every CTA must be co-resident (cooperative launch, 2 CTAs per SM).  0 = use
+// another path (M3S_GN_CHOL=steps|fused, no cooperative launch, or more tiles than resident CTAs).
+static int tiles_grid_size(m3s_gn_plan* plan) {
+    if (plan->tiles_grid >= 0) return plan->tiles_grid;
+    plan->tiles_grid = 0;
+    const char* e = getenv("M3S_GN_CHOL");
+    if (e && (strcmp(e, "steps") == 0 || strcmp(e, "fused") == 0)) return 0;
+    int coop = 0, sms = 0, per_sm = 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, plan->device);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, plan->device);
+    if (!coop || sms <= 0 ||
+        cudaFuncSetAttribute(chol_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)sizeof(TilesSmem)) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chol_tiles_kernel, kTlThreads,
+                                                      sizeof(TilesSmem)) != cudaSuccess ||
+        per_sm < 1) {
+        cudaGetLastError();
+        return 0;
+    }
+    const int nt = (plan->np + kTS - 1) / kTS;
+    const int grid = nt + nt * (nt - 1) / 2;
+    if (grid > sms * per_sm) return 0;
+    plan->tiles_grid = grid;
+    return grid;
+}
+
+// assemble + blocked factorisation of the augmented matrix, enqueued on `st`: one cooperative launch
+// (chol_tiles_kernel, or chol_fused_kernel on request) or, as the fallback, one launch per block step
 static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
     if (int rc = m3s_gn_assemble(plan, reinterpret_cast<m3s_stream_t>(st))) return rc;
     const int np = plan->np;
     const int nblk = np / kNB;
+    if (const int grid = tiles_grid_size(plan)) {
+        const int nt = (np + kTS - 1) / kTS;
+        M3S_CUDA(cudaMemsetAsync(plan->tctl, 0, sizeof(unsigned) * tl_ctl_words(nt), st));
+        int first_diag = std::max(0, std::min(sm_count_current(), grid) - nt);
+        void* args[] = {&plan->status, &plan->Hm, &plan->Lm, &plan->Linv, const_cast<int*>(&np),
+                        &plan->tctl, &first_diag, &plan->timeline};
+        M3S_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(chol_tiles_kernel), dim3(grid),
+                                             dim3(kTlThreads), args, sizeof(TilesSmem), st));
+        return launch_ok("chol_tiles_kernel");
+    }
     if (const int grid = fused_grid_size(plan)) {
         M3S_CUDA(cudaMemsetAsync(plan->gbar, 0, 64, st));
         void* args[] = {&plan->status, &plan->Hm, &plan->Lm, &plan->Ldiag, &plan->Linv,
@@ -2833,6 +3458,12 @@ static void build_solve_graph(m3s_gn_plan* plan) {
     cudaStreamDestroy(cs);
 }
 
+M3S_API int m3s_gn_plan_factor_path(m3s_gn_plan* plan) {
+    if (!plan || plan->F == 0) return 0;
+    if (tiles_grid_size(plan) > 0) return 2;
+    return fused_grid_size(plan) > 0 ? 1 : 0;
+}
+
 M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_stream_t stream) {
     M3S_REQUIRE(plan && gp, "gn_solve_update: null pointer");
     if (plan->F == 0) return M3S_OK;
@@ -2840,7 +3471,8 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
     const int np = plan->np;
     // (the cooperative launch is not captured: the graph only pays off for the ~90 launches of the
     // launch-per-step path)
-    if (!plan->graph_exec && !plan->graph_failed && np > 2 * kNB && fused_grid_size(plan) == 0)
+    if (!plan->graph_exec && !plan->graph_failed && np > 2 * kNB && tiles_grid_size(plan) == 0 &&
+        fused_grid_size(plan) == 0)
         build_solve_graph(plan);
     if (plan->graph_exec) {
         M3S_CUDA(cudaGraphLaunch(plan->graph_exec, st));

@@ -50,6 +50,43 @@ def main():
     t0 = tl[tl > 0].min()
     tl = (tl - t0) * 1e-3  # us
     ph = np.where(ph > 0, (ph - t0) * 1e-3, np.nan)
+    path = int(lib.m3s_gn_plan_factor_path(plan.handle))
+    if path == 2:
+        # dataflow factorisation: stamps of the diagonal CTAs only
+        #   tl[0, k]   = elimination of diagonal block k: [start, flags published]
+        #   ph[0, k, 0] = M_k computed; ph[0, k, 3..6] = CTA d = k/2 + 1 consuming M_k: wait start, M_k seen,
+        #   panel computed, its tiles up to date
+        d = tl[0]
+        print("block  elim[start  M done  published]   next CTA [wait  seen  panel  tiles]")
+        for kb in list(range(0, 8)) + list(range(20, 24)) + list(range(nblk - 4, nblk)):
+            print(f"{kb:4d}   {d[kb, 0]:8.1f} {ph[0, kb, 0]:8.1f} {d[kb, 1]:8.1f}      "
+                  + " ".join(f"{ph[0, kb, i]:8.1f}" for i in (3, 4, 5, 6)))
+        nt = (nblk + 1) // 2
+        print("SM of the diagonal CTAs:", [int(v) for v in raw[16 * nblk: 16 * nblk + nt]])
+        sm_of = raw[16 * nblk + 120: 16 * nblk + 352].astype(int) - 1
+        sm_of = sm_of[sm_of >= 0]
+        if sm_of.size:
+            cnt = np.bincount(sm_of, minlength=160)
+            dsm = [int(v) for v in raw[16 * nblk: 16 * nblk + nt]]
+            print("CTAs resident on the SMs of the diagonal CTAs:", [int(cnt[v]) for v in dsm],
+                  "| SMs with 0/1/2 CTAs:", [int((cnt[:148] == k).sum()) for k in (0, 1, 2)])
+        dbg = raw[16 * nblk + 64: 16 * nblk + 64 + 49]
+        if dbg[48] > 0:
+            for nm, off in (("chain", 0), ("inverse", 16), ("helper", 32)):
+                v = dbg[off:off + 16] - dbg[48]
+                print(f"first elimination of diagonal CTA 3 (block 6), clk since entry, {nm:8s}:", " ".join(f"{int(x):5d}" if x > 0 else "    -" for x in v))
+        el = ph[0, :, 0] - d[:, 0]
+        pub = d[:, 1] - ph[0, :, 0]
+        hop = ph[0, :, 4] - d[:, 1]
+        pan = ph[0, :, 5] - ph[0, :, 4]
+        upd = ph[0, :, 6] - ph[0, :, 5]
+        print("means (us): elim32 %.2f | stores + publish %.2f | flag hop %.2f | panel %.2f | tile updates %.2f"
+              % (np.nanmean(el), np.nanmean(pub), np.nanmean(hop[1::2]), np.nanmean(pan), np.nanmean(upd)))
+        print(f"factorisation: {d[nblk - 1, 1] - d[0, 0]:.1f} us = {(d[nblk - 1, 1] - d[0, 0]) / nblk:.2f} us per block step")
+        b = tl[3]
+        print(f"back-substitution: first CTA start {b[:, 0].min():.1f} us, block 0 published at {b[0, 1]:.1f} us "
+              f"({b[0, 1] - b[:, 0].min():.1f} us, {(b[0, 1] - b[nblk - 1, 1]) / max(nblk - 1, 1):.2f} us per block)")
+        return
     names = ["diag", "tile-solve", "tile-upd", "backsolve"]
     for k, nm in enumerate(names):
         d = tl[k]
