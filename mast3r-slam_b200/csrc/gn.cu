@@ -2170,7 +2170,7 @@ __device__ __forceinline__ void tl_rowdot(const double (*P)[kPP], const double* 
 //           columns X, Y, the multipliers M1, M2 and the pivots of every pair through shared memory;
 //   inverse N = L^-1 and M = D^-1/2 N from the published multipliers (lane = column, registers);
 //   helper  owns the columns of the segments the chain has not reached yet, applies every published pair
-//           to them and hands a segment over through `hs` two pairs before the chain needs it.
+//           to them and hands the next segment over through `hs` when the chain gets there.
 // What shaped this code (clock stamps per pair via `dbg`, profiles/microbench/elim_bench.cu):
 //   * with all 32 columns in the chain warp's registers ptxas scheduled ~60 trailing DFMAs in front of
 //     each determinant (in-order issue: 450 clk per pair) -> trailing update on the helper warp;
@@ -2216,24 +2216,21 @@ __device__ __noinline__ void tl_elim32_w(TilesSmem& sm, double (*Tm)[kTP], int o
     volatile int* hsf = &sm.hsflag;
     if (dbg != nullptr && warp == 0 && lane == 0) dbg[48] = clock64();
     if (warp == 0) {
-        // a[]: the 8 columns of the current segment; b[]: the next segment's, received from warp 2 TWO pairs
-        // before the chain gets there (the hand-over latency, ~400 clk, hides behind pairs 2 and 3, whose
-        // updates of those columns the chain then applies itself)
-        double a[8], b[8];
+        double a[8];   // the 8 columns of the current segment
         bool isbad = false;
 #pragma unroll
-        for (int c = 0; c < 8; ++c) { a[c] = Tm[o + c][o + lane]; b[c] = 0.0; }   // W[lane][c] by symmetry: conflict-free
+        for (int c = 0; c < 8; ++c) a[c] = Tm[o + c][o + lane];   // W[lane][c] by symmetry: conflict-free
 #pragma unroll 1
         for (int s = 0; s < 4; ++s) {
+            if (s > 0) {
+                while (*hsf < s) { TL_SPIN_PAUSE }
+                __syncwarp();
+#pragma unroll
+                for (int c = 0; c < 8; ++c) a[c] = hs[c * 32 + lane];
+            }
 #pragma unroll
             for (int p = 0; p < 4; ++p) {
                 const int q = 4 * s + p, j = 2 * q;
-                if (p == 2 && s < 3) {
-                    while (*hsf < s + 1) { TL_SPIN_PAUSE }
-                    __syncwarp();
-#pragma unroll
-                    for (int c = 0; c < 8; ++c) b[c] = hs[c * 32 + lane];
-                }
                 // The pivot block and the pivot-column entries of the rows that follow go through SHARED
                 // MEMORY (store own x, y -> __syncwarp -> broadcast loads), not through shuffles (30 SHFL per
                 // pair cost more issue slots and, measured inside the factorisation kernel, far more time).
@@ -2244,22 +2241,13 @@ __device__ __noinline__ void tl_elim32_w(TilesSmem& sm, double (*Tm)[kTP], int o
                 double al = X[q * 32 + j];
                 double be = X[q * 32 + j + 1];
                 double ga = Y[q * 32 + j + 1];
-                double xc[8], yc[8], xn[8], yn[8];
+                double xc[8], yc[8];
 #pragma unroll
                 for (int c = 2 * p + 2; c < 8; c += 2) {
                     const double2 xv = *reinterpret_cast<const double2*>(X + q * 32 + 8 * s + c);
                     const double2 yv = *reinterpret_cast<const double2*>(Y + q * 32 + 8 * s + c);
                     xc[c] = xv.x; xc[c + 1] = xv.y;
                     yc[c] = yv.x; yc[c + 1] = yv.y;
-                }
-                if (p >= 2 && s < 3) {
-#pragma unroll
-                    for (int c = 0; c < 8; c += 2) {
-                        const double2 xv = *reinterpret_cast<const double2*>(X + q * 32 + 8 * s + 8 + c);
-                        const double2 yv = *reinterpret_cast<const double2*>(Y + q * 32 + 8 * s + 8 + c);
-                        xn[c] = xv.x; xn[c + 1] = xv.y;
-                        yn[c] = yv.x; yn[c + 1] = yv.y;
-                    }
                 }
                 double det = fma(al, ga, -(be * be));
                 if (!(al > 1e-290) || !(det > 1e-300) || !(det < 1e300)) {  // warp-uniform
@@ -2273,21 +2261,12 @@ __device__ __noinline__ void tl_elim32_w(TilesSmem& sm, double (*Tm)[kTP], int o
                     const double z = fma(n1, xc[c], n2 * yc[c]);                        // independent of r
                     a[c] = fma(-r, z, a[c]);                                            // ONE op after the reciprocal
                 }
-                if (p >= 2 && s < 3) {
-#pragma unroll
-                    for (int c = 0; c < 8; ++c) {
-                        const double z = fma(n1, xn[c], n2 * yn[c]);
-                        b[c] = fma(-r, z, b[c]);
-                    }
-                }
                 M1[q * 32 + lane] = n1 * r;
                 M2[q * 32 + lane] = n2 * r;
                 if (lane == 0) { sm.piv[q][0] = al; sm.piv[q][1] = be; sm.piv[q][2] = det; }
                 __syncwarp();
                 if (lane == 0) { TL_FENCE_BLOCK *prog = q + 1; if (dbg != nullptr) dbg[q] = clock64(); }
             }
-#pragma unroll
-            for (int c = 0; c < 8; ++c) a[c] = b[c];
         }
         if (isbad && lane == 0) sm.bad = 1;
     } else if (warp == 1) {
@@ -2323,30 +2302,29 @@ __device__ __noinline__ void tl_elim32_w(TilesSmem& sm, double (*Tm)[kTP], int o
         double h[24];   // columns 8 .. 31 of row `lane`
 #pragma unroll
         for (int c = 0; c < 24; ++c) h[c] = Tm[o + 8 + c][o + lane];
-        // Loop over the pairs fully unrolled (static register indices).  Segment sg + 1 is handed over after
-        // pair 4 sg + 1 -- two pairs before the chain needs it; the chain applies pairs 4 sg + 2, 4 sg + 3 to
-        // it itself -- and those 8 columns are updated and published first, the rest afterwards.
+        // loop over the pairs fully unrolled (static register indices); in the pair that ends a segment the
+        // 8 columns handed over next are updated and published first, the rest afterwards.  (Handing a
+        // segment over two pairs early, with the chain applying the last two pairs itself, was measured
+        // slower: 7 800 vs 6 200 clk stand-alone -- the helper's pace, not the hop, bounds the hand-over.)
 #pragma unroll
-        for (int q = 0; q < 10; ++q) {
+        for (int q = 0; q < 12; ++q) {
             while (*prog < q + 1) { TL_SPIN_PAUSE }
             __syncwarp();
             const double m1 = M1[q * 32 + lane], m2 = M2[q * 32 + lane];
             const double2* Xq = reinterpret_cast<const double2*>(X + q * 32);
             const double2* Yq = reinterpret_cast<const double2*>(Y + q * 32);
-            const int sg = q / 4;
-            // first column still owned here: segment sg + 1 until it is handed over (after q % 4 == 1)
-            const int c0 = ((q & 3) <= 1) ? 8 * (sg + 1) : 8 * (sg + 2);
+            const int c0 = 8 * (q / 4 + 1);   // first column still owned here
 #pragma unroll
-            for (int c = c0; c < c0 + 8 && c < kNB; c += 2) {
+            for (int c = c0; c < c0 + 8; c += 2) {
                 const double2 xv = Xq[c >> 1], yv = Yq[c >> 1];
                 h[c - 8] = fma(-m2, yv.x, fma(-m1, xv.x, h[c - 8]));
                 h[c - 7] = fma(-m2, yv.y, fma(-m1, xv.y, h[c - 7]));
             }
-            if ((q & 3) == 1) {
+            if ((q & 3) == 3) {
 #pragma unroll
                 for (int c = 0; c < 8; ++c) hs[c * 32 + lane] = h[c0 - 8 + c];
                 __syncwarp();
-                if (lane == 0) { TL_FENCE_BLOCK *hsf = sg + 1; }
+                if (lane == 0) { TL_FENCE_BLOCK *hsf = q / 4 + 1; }
             }
 #pragma unroll
             for (int c = c0 + 8; c < kNB; c += 2) {
@@ -2738,6 +2716,165 @@ gn_backsolve_update_kernel(Status* __restrict__ status, const double* __restrict
     __syncthreads();
     if (tid == 0) { st_release(flags + b, epoch); tl_stamp(tl, (3 * nblk + b) * 2 + 1); }
     if (b != 0) return;
+
+    // ---- block 0: all of x is published (x_0 depended on every other block) ----------------------
+    __shared__ double red[kBackThreads / 32];
+    __shared__ int decision;  // 0 apply, 1 stop, 2 fail
+    double psum = 0.0;
+    int nonfinite = 0;
+    for (int i = tid; i < dim; i += kBackThreads) {
+        const double v = __ldcg(xsol + i);
+        dx_out[i] = v;
+        psum += v * v;
+        if (!(fabs(v) <= 1.7e308)) nonfinite = 1;
+    }
+    psum = warp_sum(psum);
+    nonfinite = __any_sync(0xffffffffu, nonfinite);
+    if ((tid & 31) == 0) red[tid >> 5] = nonfinite ? __longlong_as_double(0x7ff8000000000000LL) : psum;
+    __syncthreads();
+    if (tid == 0) {
+        double s = 0.0;
+        for (int w = 0; w < kBackThreads / 32; ++w) s += red[w];
+        const double nrm = sqrt(s);
+        status->last_norm = nrm;
+        status->attempted += 1;
+        int d;
+        if (!(nrm == nrm)) d = 2;                 // non-finite step: treat as failed solve
+        else if (nrm < delta_thresh) d = 1;       // converged: do not apply
+        else d = 0;
+        if (d == 1) status->stopped = 1;
+        if (d == 2) status->failed = 1;
+        if (d == 0) status->applied += 1;
+        decision = d;
+    }
+    __syncthreads();
+    if (decision != 0) return;
+    for (int f = tid; f < num_free; f += kBackThreads) {
+        double xi[7];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) xi[k] = __ldcg(xsol + 7 * f + k);
+        if (metal) sim3_retract_metal_dev(xi, poses + 8 * free_kf[f]);
+        else sim3_retract_dev(xi, poses + 8 * free_kf[f]);
+    }
+}
+
+// Grouped variant (default): one CTA per kBackGroup = 4 consecutive 32-column blocks, so the chain has one
+// flag hop per 128 columns instead of one per 32 (a hop = fence + flag + remote poll + 256-B read, ~1.5 us;
+// the arithmetic between two hops is ~0.3 us).  CTA gi owns blocks b_hi = nblk-1-4 gi down to b_lo; it
+// accumulates s_b = sum_{r > b_hi} L[r, b]^T x_r for its blocks as the groups above publish, then walks its
+// own blocks top-down inside shared memory.  Same flags / epoch / decision / retraction as the kernel above.
+constexpr int kBackGroup = 4;
+
+__global__ void __launch_bounds__(kBackThreads)
+gn_backsolve_group_kernel(Status* __restrict__ status, const double* __restrict__ Lm,
+                          const double* __restrict__ Linv, int np, int dim, int num_free,
+                          const int* __restrict__ free_kf, double delta_thresh,
+                          double* __restrict__ xsol, int* __restrict__ flags, int epoch,
+                          double* __restrict__ dx_out, double* __restrict__ poses,
+                          long long* __restrict__ tl, int metal) {
+    if (status->stopped | status->failed) return;
+    const int nblk = np / kNB;
+    const int gi = blockIdx.x;
+    const int ngroups = (nblk + kBackGroup - 1) / kBackGroup;
+    const int b_hi = nblk - 1 - kBackGroup * gi;
+    const int b_lo = max(b_hi - kBackGroup + 1, 0);
+    const int nb = b_hi - b_lo + 1;                  // blocks of this group (the last group may be short)
+    const int tid = threadIdx.x;
+    if (tid == 0) tl_stamp(tl, (3 * nblk + b_hi) * 2);
+    if (status->chol_fail) {
+        if (gi == ngroups - 1 && tid == 0) { status->failed = 1; status->attempted += 1; }
+        return;
+    }
+    __shared__ double Li[kBackGroup][kNB][kNB + 1];        // M of the group's blocks (index 0 = b_hi)
+    __shared__ double xr[kBackGroup][kNB];                 // x of the group being applied / of this group
+    __shared__ double part[kBackThreads / 32][kNB];
+    __shared__ double rhs[kNB];
+    __shared__ int ok_s;
+    const int c = tid & 31, g = tid >> 5;                  // column c of a block, row group g (4 rows)
+    for (int i = tid; i < nb * kNB * kNB; i += kBackThreads) {
+        const int q = i / (kNB * kNB), e = i % (kNB * kNB);
+        Li[q][e / kNB][e % kNB] = Linv[(size_t)(b_hi - q) * kNB * kNB + e];
+    }
+    double acc[kBackGroup];
+#pragma unroll
+    for (int q = 0; q < kBackGroup; ++q) acc[q] = 0.0;
+    // contributions of the groups above, as they are published
+    for (int gr = 0; gr < gi; ++gr) {
+        const int r_hi = nblk - 1 - kBackGroup * gr;
+        // tiles L[r, b] of this group's columns for the 4 blocks r of group gr: rows 4g .. 4g+3 of column c
+        double t[kBackGroup][kBackGroup][4];
+#pragma unroll
+        for (int rr = 0; rr < kBackGroup; ++rr)
+#pragma unroll
+            for (int q = 0; q < kBackGroup; ++q)
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    t[rr][q][i] = (q < nb) ? Lm[(size_t)((r_hi - rr) * kNB + 4 * g + i) * np + (b_hi - q) * kNB + c] : 0.0;
+        if (tid == 0) {
+            int spins = 0, okv = 1;
+            while (ld_acquire(flags + gr) != epoch) {
+                if (++spins > kSpinLimit) { okv = 0; break; }
+            }
+            ok_s = okv;
+        }
+        __syncthreads();
+        if (!ok_s) {  // cannot happen with in-order dispatch; never hang the device
+            if (tid == 0) status->failed = 1;
+            return;
+        }
+        if (tid < kBackGroup * kNB) xr[tid >> 5][tid & 31] = __ldcg(xsol + (r_hi - (tid >> 5)) * kNB + (tid & 31));
+        __syncthreads();
+#pragma unroll
+        for (int rr = 0; rr < kBackGroup; ++rr)
+#pragma unroll
+            for (int q = 0; q < kBackGroup; ++q)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[q] = fma(t[rr][q][i], xr[rr][4 * g + i], acc[q]);
+        __syncthreads();  // xr is rewritten in the next round
+    }
+    // inside the group, top-down (unrolled: acc[] stays in registers; nb is uniform over the CTA)
+#pragma unroll
+    for (int q = 0; q < kBackGroup; ++q) {
+        if (q >= nb) break;
+        const int b = b_hi - q;
+        part[g][c] = acc[q];
+        __syncthreads();
+        if (tid < kNB) {
+            double s = 0.0;
+#pragma unroll
+            for (int w = 0; w < kBackThreads / 32; ++w) s += part[w][tid];
+            rhs[tid] = Lm[(size_t)np * np + b * kNB + tid] - s;  // y_b - s_b
+        }
+        __syncthreads();
+        {   // x_b[i] = sum_r M[r][i] rhs[r]: 8 partial sums of 4 terms per output
+            double s = 0.0;
+#pragma unroll
+            for (int m = 0; m < 4; ++m) s = fma(Li[q][4 * g + m][c], rhs[4 * g + m], s);
+            part[g][c] = s;
+        }
+        __syncthreads();
+        if (tid < kNB) {
+            double s = 0.0;
+#pragma unroll
+            for (int w = 0; w < kBackThreads / 32; ++w) s += part[w][tid];
+            xr[q][tid] = s;
+            __stcg(xsol + b * kNB + tid, s);
+        }
+        __syncthreads();
+        // x_b into the sums of the group's lower blocks: tile L[b, b'] rows 4g .. 4g+3, column c
+#pragma unroll
+        for (int q2 = q + 1; q2 < kBackGroup; ++q2) {
+            if (q2 >= nb) break;
+            double s = acc[q2];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                s = fma(Lm[(size_t)(b * kNB + 4 * g + i) * np + (b_hi - q2) * kNB + c], xr[q][4 * g + i], s);
+            acc[q2] = s;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) { __threadfence(); st_release(flags + gi, epoch); tl_stamp(tl, (3 * nblk + b_lo) * 2 + 1); }
+    if (b_lo != 0) return;
 
     // ---- block 0: all of x is published (x_0 depended on every other block) ----------------------
     __shared__ double red[kBackThreads / 32];
@@ -3479,10 +3616,21 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
     } else {
         if (int rc = enqueue_assemble_factor(plan, st)) return rc;
     }
-    gn_backsolve_update_kernel<<<np / kNB, kBackThreads, 0, st>>>(
-        plan->status, plan->Lm, plan->Linv, np, plan->dim, plan->F, plan->free_kf, gp->delta_thresh,
-        plan->xsol, plan->flags, 1, plan->dx, plan->poses, plan->timeline,
-        gp->semantics == M3S_SEM_METAL ? 1 : 0);
+    static const bool per_block = [] {   // M3S_GN_BACKSOLVE=block: one CTA per 32-column block (round 1)
+        const char* e = getenv("M3S_GN_BACKSOLVE");
+        return e && strcmp(e, "block") == 0;
+    }();
+    const int nblk = np / kNB;
+    if (per_block)
+        gn_backsolve_update_kernel<<<nblk, kBackThreads, 0, st>>>(
+            plan->status, plan->Lm, plan->Linv, np, plan->dim, plan->F, plan->free_kf, gp->delta_thresh,
+            plan->xsol, plan->flags, 1, plan->dx, plan->poses, plan->timeline,
+            gp->semantics == M3S_SEM_METAL ? 1 : 0);
+    else
+        gn_backsolve_group_kernel<<<(nblk + kBackGroup - 1) / kBackGroup, kBackThreads, 0, st>>>(
+            plan->status, plan->Lm, plan->Linv, np, plan->dim, plan->F, plan->free_kf, gp->delta_thresh,
+            plan->xsol, plan->flags, 1, plan->dx, plan->poses, plan->timeline,
+            gp->semantics == M3S_SEM_METAL ? 1 : 0);
     return launch_ok("gn_backsolve_update_kernel");
 }
 
