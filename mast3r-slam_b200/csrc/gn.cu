@@ -3616,10 +3616,9 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
     } else {
         if (int rc = enqueue_assemble_factor(plan, st)) return rc;
     }
-    static const bool per_block = [] {   // M3S_GN_BACKSOLVE=block: one CTA per 32-column block (round 1)
-        const char* e = getenv("M3S_GN_BACKSOLVE");
-        return e && strcmp(e, "block") == 0;
-    }();
+    // M3S_GN_BACKSOLVE=block: one CTA per 32-column block (round 1); read per call (A/B, tests)
+    const char* bse = getenv("M3S_GN_BACKSOLVE");
+    const bool per_block = bse && strcmp(bse, "block") == 0;
     const int nblk = np / kNB;
     if (per_block)
         gn_backsolve_update_kernel<<<nblk, kBackThreads, 0, st>>>(

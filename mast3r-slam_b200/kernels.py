@@ -439,6 +439,12 @@ class GNPlan:
         """[num_kf, 8] fp64 pose state of the solver (before the final float32 cast)."""
         return self._view(self._lib.m3s_gn_plan_poses(self.handle), 8 * self.num_kf).view(-1, 8)
 
+    def factor_path(self) -> int:
+        """0 = one launch per block step, 1 = persistent chain + workers, 2 = dataflow over
+        shared-memory-resident tiles (m3s_gn_plan_factor_path; decided at the first solve of the plan
+        from M3S_GN_CHOL and what is co-resident on the device)"""
+        return int(_lib.load().m3s_gn_plan_factor_path(self.handle))
+
     def dx(self) -> torch.Tensor:
         return self._view(self._lib.m3s_gn_plan_dx(self.handle), self.dim)
 

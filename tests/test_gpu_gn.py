@@ -327,3 +327,48 @@ def test_gn_gated_points_cannot_poison(K, synth, mode):
     h["Xs"] = Xs.reshape(h["Xs"].shape)
     out = fn(*[h[k] for k in ("Twc", "Xs", "Cs", "ii", "jj", "idx", "valid", "Q")], max_iter=4)
     assert np.array_equal(out, clean)
+
+
+@pytest.mark.parametrize("num_kf,loops", [(6, 2), (24, 5), (40, 10), (200, 103)])
+def test_solve_paths_agree(K, synth, monkeypatch, num_kf, loops, precision):
+    """The three factorisations (launch per block step, persistent chain + workers, dataflow over
+    shared-memory-resident tiles) and both back-substitutions (one CTA per 32-column block / per group of
+    four) solve the same damped system: dx agrees to round-off, poses to 1e-5 of the update.  Covers one
+    tile (np = 64), odd numbers of 32-column blocks (np = 288: the last tile is half padding) and the
+    200-keyframe system of config 5 (44 blocks, 253 CTAs)."""
+    import ctypes as C
+    import torch
+    from mast3r_slam_b200 import _lib
+    if precision != "f64":
+        pytest.skip("the solve is independent of the accumulate precision")
+    g = synth.make_graph(11, num_kf, loops, 48, 64, num_pts=1024)
+    dev = torch.device("cuda", 0)
+    t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a)).to(dev, dt)  # noqa: E731
+    Twc, Xs, Cs = t(g["Twc"], torch.float32), t(g["Xs"], torch.float32), t(g["Cs"], torch.float32)
+    idx, valid, Q = t(g["idx"], torch.int32), t(g["valid"].astype(np.uint8), torch.uint8), t(g["Q"], torch.float32)
+    params = K.make_params(_lib.GN_POINTS, 1, 1, 0.0, 0.0, 1.5, 0.01)
+    lib = _lib.load()
+    p = lambda x: C.c_void_p(x.data_ptr())  # noqa: E731
+    res = {}
+    for chol, back in (("steps", "block"), ("steps", "group"), ("fused", "group"), ("tiles", "group"), ("tiles", "block")):
+        monkeypatch.setenv("M3S_GN_CHOL", chol)
+        monkeypatch.setenv("M3S_GN_BACKSOLVE", back)
+        plan = K.GNPlan(g["ii"], g["jj"], num_kf, 1024, 1, dev)
+        _lib.check(lib.m3s_gn_set_poses(plan.handle, p(Twc), None))
+        _lib.check(lib.m3s_gn_accumulate(plan.handle, C.byref(params), p(Xs), p(Cs), p(idx), p(valid), p(Q),
+                                         0, plan.E, None))
+        _lib.check(lib.m3s_gn_solve_update(plan.handle, C.byref(params), None))
+        torch.cuda.synchronize()
+        st = plan.status()
+        assert st["applied"] == 1 and not st["failed"], (chol, back, st)
+        res[(chol, back)] = (plan.factor_path(), plan.dx().cpu().numpy().copy(), plan.poses().cpu().numpy().copy())
+        del plan
+    assert res[("steps", "block")][0] == 0 and res[("tiles", "group")][0] == 2
+    ref_dx, ref_pose = res[("steps", "block")][1:]
+    scale = np.abs(ref_dx).max()
+    for key, (_, dx, pose) in res.items():
+        assert np.abs(dx - ref_dx).max() <= 1e-8 * scale, key
+        assert np.abs(pose - ref_pose).max() <= 1e-9 * max(np.abs(ref_pose).max(), 1.0), key
+    # the grouped back-substitution reads the same factor: bitwise equal to the per-block one
+    assert np.array_equal(res[("tiles", "group")][1], res[("tiles", "block")][1]) or \
+        np.abs(res[("tiles", "group")][1] - res[("tiles", "block")][1]).max() <= 1e-12 * scale
