@@ -442,3 +442,33 @@ def test_iter_proj_very_wide_image(K, oracle):
     p, v = K.iter_proj(rays, pts, p0, 3, 1e-8, 1e-6)
     po, vo = oracle.iter_proj(rays, pts, p0, 3, 1e-8, 1e-6)
     assert np.array_equal(p, po) and np.array_equal(v, vo)
+
+
+@pytest.mark.parametrize("impl", ["tile", "cache", "quad", "generic"])
+def test_iter_proj_extreme_determinants(K, oracle, synth, monkeypatch, impl):
+    """The LM step divides by det = a d - b^2 clamped at 1e-10 (kernels.py:217-222).  The kernels take the
+    fast path of the IEEE division below 1e30 and the library division above; gradients scaled so that det
+    lands on both sides of that guard, overflows to inf, or turns NaN must all give the reference's bits."""
+    monkeypatch.setenv("M3S_ITER_PROJ_IMPL", impl)
+    h, w = 32, 64
+    pair = synth.make_pair(21, h, w, 24, "dyadic")
+    rays, pts, p0 = oracle.prep_for_iter_proj(pair["X11"][None], pair["X21"][None], None)
+    rng = np.random.default_rng(5)
+    for scale in (1e3, 3e6, 1e8, 1e10, 3e10):   # det ~ scale^4 x 3e-11: 3e1 .. 2e31 (both sides of the guard)
+        r = rays.copy()
+        r[..., 3:] *= np.float32(scale)
+        p, v = K.iter_proj(r, pts, p0, 4, 1e-8, 1e-6)
+        with np.errstate(all="ignore"):
+            po, vo = oracle.iter_proj(r, pts, p0, 4, 1e-8, 1e-6)
+        fin = np.isfinite(po).all(-1)          # numpy cannot index with the NaN positions a blown-up step leaves
+        assert np.array_equal(p[fin], po[fin]) and np.array_equal(v[fin], vo[fin]), scale
+    # per-pixel mixture of scales in one image incl. det = inf and inf - inf = NaN; ONE iteration, so that no
+    # NaN position reaches the sampler (numpy raises on those, the C oracle cannot index them either)
+    r = rays.copy()
+    mix = rng.choice(np.array([1.0, 1e4, 1e7, 3e9, 1e12, 1e19], np.float32), size=r.shape[:3])
+    r[..., 3:] *= mix[..., None]
+    p, v = K.iter_proj(r, pts, p0, 1, 1e-8, 1e-6)
+    with np.errstate(all="ignore"):
+        po, vo = oracle.iter_proj(r, pts, p0, 1, 1e-8, 1e-6)
+    same = (p == po) | (np.isnan(p) & np.isnan(po))
+    assert same.all() and np.array_equal(v, vo)
