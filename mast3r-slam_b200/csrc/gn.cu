@@ -2131,6 +2131,36 @@ __device__ __forceinline__ void tl_gemm_nt(const double* A, int lda, const doubl
             for (int j = 0; j < NJ; ++j) acc[i][j] = fma(a[i].y, b[j].y, fma(a[i].x, b[j].x, acc[i][j]));
     }
 }
+// the same for a SYMMETRIC product A A^T of which only the lower triangle is kept: register tiles with
+// i < j lie above the diagonal (rows ty + 16 i < columns tx + 16 j) and are skipped -- 10 of 16 tiles
+template <int MI>
+__device__ __forceinline__ void tl_syrk_lower(const double* A, int lda, double (&acc)[MI][MI]) {
+    const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j < MI; ++j) acc[i][j] = 0.0;
+#pragma unroll 4
+    for (int k = 0; k < kNB; k += 2) {
+        double2 a[MI], b[MI];
+#pragma unroll
+        for (int i = 0; i < MI; ++i) a[i] = *reinterpret_cast<const double2*>(A + (ty + 16 * i) * lda + k);
+#pragma unroll
+        for (int j = 0; j < MI; ++j) b[j] = *reinterpret_cast<const double2*>(A + (tx + 16 * j) * lda + k);
+#pragma unroll
+        for (int i = 0; i < MI; ++i)
+#pragma unroll
+            for (int j = 0; j <= i; ++j) acc[i][j] = fma(a[i].y, b[j].y, fma(a[i].x, b[j].x, acc[i][j]));
+    }
+}
+template <int MI>
+__device__ __forceinline__ void tl_sub_lower(double* Cm, int ldc, const double (&acc)[MI][MI]) {
+    const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j <= i; ++j) Cm[(ty + 16 * i) * ldc + tx + 16 * j] -= acc[i][j];
+}
 template <int MI, int NJ>
 __device__ __forceinline__ void tl_sub(double* Cm, int ldc, const double (&acc)[MI][NJ]) {
     const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
@@ -2219,7 +2249,7 @@ __device__ __noinline__ void tl_elim32_w(TilesSmem& sm, double (*Tm)[kTP], int o
         double a[8];   // the 8 columns of the current segment
         bool isbad = false;
 #pragma unroll
-        for (int c = 0; c < 8; ++c) a[c] = Tm[o + c][o + lane];   // W[lane][c] by symmetry: conflict-free
+        for (int c = 0; c < 8; ++c) a[c] = Tm[o + lane][o + c];   // row `lane`; only entries c <= lane (lower triangle) are ever used
 #pragma unroll 1
         for (int s = 0; s < 4; ++s) {
             if (s > 0) {
@@ -2301,7 +2331,7 @@ __device__ __noinline__ void tl_elim32_w(TilesSmem& sm, double (*Tm)[kTP], int o
     } else if (warp == 2) {
         double h[24];   // columns 8 .. 31 of row `lane`
 #pragma unroll
-        for (int c = 0; c < 24; ++c) h[c] = Tm[o + 8 + c][o + lane];
+        for (int c = 0; c < 24; ++c) h[c] = Tm[o + lane][o + 8 + c];
         // loop over the pairs fully unrolled (static register indices); in the pair that ends a segment the
         // 8 columns handed over next are updated and published first, the rest afterwards.  (Handing a
         // segment over two pairs early, with the chain applying the last two pairs itself, was measured
@@ -2400,10 +2430,10 @@ chol_tiles_kernel(Status* __restrict__ status, const double* __restrict__ Hm, do
             if (tid < kNB) sm.yk[tid] = __ldcg(ybase + k * kNB + tid);
             __syncthreads();
             if (last && tid == 0) tl_stamp(tl, 8 * nblk + 8 * k + 5);
-            {
+            {   // only the lower triangle of the diagonal tile is kept up to date (and read)
                 double acc[4][4];
-                tl_gemm_nt<4, 4>(&sm.PA[0][0], kPP, &sm.PA[0][0], kPP, acc);
-                tl_sub<4, 4>(&sm.T[0][0], kTP, acc);
+                tl_syrk_lower<4>(&sm.PA[0][0], kPP, acc);
+                tl_sub_lower<4>(&sm.T[0][0], kTP, acc);
             }
             tl_rowdot(sm.PA, sm.yk, sm.rhs, kTS, true);
             __syncthreads();
@@ -2431,8 +2461,8 @@ chol_tiles_kernel(Status* __restrict__ status, const double* __restrict__ Hm, do
             if (second) {
                 tl_store_panel(sm.PA, Lm, np, r0 + kNB, k, kNB);
                 double acc[2][2];
-                tl_gemm_nt<2, 2>(&sm.PA[0][0], kPP, &sm.PA[0][0], kPP, acc);
-                tl_sub<2, 2>(&sm.T[kNB][kNB], kTP, acc);
+                tl_syrk_lower<2>(&sm.PA[0][0], kPP, acc);
+                tl_sub_lower<2>(&sm.T[kNB][kNB], kTP, acc);
                 tl_rowdot(sm.PA, sm.yk, sm.rhs + kNB, kNB, true);
             }
             if (tid == 0) { sm.prog = 0; sm.hsflag = 0; }
