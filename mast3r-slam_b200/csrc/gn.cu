@@ -2995,6 +2995,7 @@ struct m3s_gn_plan {
     int* flags = nullptr;           // [np / 32] publication flags of the back-substitution
     unsigned* gbar = nullptr;       // grid-barrier counter of the persistent factorisation
     int fused_grid = -1;            // CTAs of chol_fused_kernel (0 = not available, -1 = not probed)
+    bool hm_clean = false;          // the structurally-zero entries of Hm are zero (see m3s_gn_assemble)
     unsigned* tctl = nullptr;       // flag words of the dataflow factorisation (chol_tiles_kernel)
     int tiles_grid = -1;            // its CTA count (0 = not available / not selected, -1 = not probed)
     long long* timeline = nullptr;  // [4, np / 32, 2] globaltimer stamps (M3S_GN_TIMELINE=1), else null
@@ -3456,9 +3457,14 @@ M3S_API int m3s_gn_assemble(m3s_gn_plan* plan, m3s_stream_t stream) {
     M3S_REQUIRE(plan, "gn_assemble: null plan");
     if (plan->F == 0) return M3S_OK;
     cudaStream_t st = as_stream(stream);
-    // NOTE: the memset is unconditional (cheap); kernels after a stop are no-ops and H is not
-    // consumed any more.
-    M3S_CUDA(cudaMemsetAsync(plan->Hm, 0, sizeof(double) * (size_t)(plan->np + 1) * plan->np, st));
+    // gn_assemble_kernel REWRITES every structurally non-zero block (and the rhs row entries of the free
+    // keyframes) on every call, so the 15.9 MB of Hm only have to be zeroed when something else wrote into
+    // them: the launch-per-step and the persistent factorisations update Hm in place, the dataflow
+    // factorisation keeps its tiles in shared memory and leaves Hm alone (hm_clean stays true).
+    if (!plan->hm_clean) {
+        M3S_CUDA(cudaMemsetAsync(plan->Hm, 0, sizeof(double) * (size_t)(plan->np + 1) * plan->np, st));
+        plan->hm_clean = true;
+    }
     M3S_CUDA(cudaMemsetAsync(plan->flags, 0, sizeof(int) * std::max(plan->np / kNB, 1), st));
     gn_assemble_kernel<<<plan->nblocks_H, 64, 0, st>>>(plan->status, plan->blocks, plan->list_edge,
                                                        plan->list_sign, plan->edge_blocks, plan->Hm,
@@ -3561,6 +3567,7 @@ static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
                                              dim3(kTlThreads), args, sizeof(TilesSmem), st));
         return launch_ok("chol_tiles_kernel");
     }
+    plan->hm_clean = false;   // both paths below factorise Hm in place
     if (const int grid = fused_grid_size(plan)) {
         M3S_CUDA(cudaMemsetAsync(plan->gbar, 0, 64, st));
         void* args[] = {&plan->status, &plan->Hm, &plan->Lm, &plan->Ldiag, &plan->Linv,
