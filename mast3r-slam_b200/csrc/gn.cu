@@ -3563,9 +3563,15 @@ static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
         int first_diag = std::max(0, std::min(sm_count_current(), grid) - nt);
         void* args[] = {&plan->status, &plan->Hm, &plan->Lm, &plan->Linv, const_cast<int*>(&np),
                         &plan->tctl, &first_diag, &plan->timeline};
-        M3S_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(chol_tiles_kernel), dim3(grid),
-                                             dim3(kTlThreads), args, sizeof(TilesSmem), st));
-        return launch_ok("chol_tiles_kernel");
+        const cudaError_t ce = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(chol_tiles_kernel), dim3(grid),
+                                                           dim3(kTlThreads), args, sizeof(TilesSmem), st);
+        if (ce == cudaSuccess) return launch_ok("chol_tiles_kernel");
+        // the device cannot hold the grid right now (e.g. SMs partitioned away from this context): use the
+        // launch-per-step path for this plan from here on -- another CUDA path, never a CPU one
+        cudaGetLastError();
+        if (ce != cudaErrorCooperativeLaunchTooLarge && ce != cudaErrorLaunchOutOfResources)
+            return cuda_fail(ce, "cudaLaunchCooperativeKernel(chol_tiles_kernel)");
+        plan->tiles_grid = 0;
     }
     plan->hm_clean = false;   // both paths below factorise Hm in place
     if (const int grid = fused_grid_size(plan)) {
