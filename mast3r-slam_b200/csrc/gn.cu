@@ -2367,15 +2367,6 @@ __device__ __noinline__ void tl_elim32_w(TilesSmem& sm, double (*Tm)[kTP], int o
     }
 }
 
-// block-wide wrapper (all 256 threads): nothing runs beside the elimination
-__device__ __forceinline__ void tl_elim32(TilesSmem& sm, double (*Tm)[kTP], int o, double* sc, double* hs,
-                                          double (*Mo)[kPP]) {
-    if (threadIdx.x == 0) { sm.prog = 0; sm.hsflag = 0; }
-    __syncthreads();
-    if (tl_is_elim_warp()) tl_elim32_w(sm, Tm, o, sc, hs, Mo, nullptr);
-    __syncthreads();
-}
-
 __global__ void __launch_bounds__(kTlThreads, 2)
 chol_tiles_kernel(Status* __restrict__ status, const double* __restrict__ Hm, double* Lm, double* Linv, int np,
                   unsigned* ctlw, int first_diag, long long* __restrict__ tl) {
