@@ -138,6 +138,24 @@ int m3s_match_iterative_proj(const float* X11, const float* X21, const float* D1
                              int dilation_max, float dist_thresh, void* workspace,
                              size_t workspace_bytes, m3s_stream_t stream);
 
+/* m3s_match_iterative_proj without a caller workspace and without any allocation: the
+ * intermediates live in a file-scope device array of the library.  No counterpart in the
+ * reference; added for callers that cannot call
+ * cudaMalloc (stream capture, tight serving loops, harnesses that forbid it).
+ *   - same arguments, results and error codes as m3s_match_iterative_proj
+ *   - B*H*W > M3S_MATCH_STATIC_MAX_PIXELS => M3S_ERR_WORKSPACE with a message naming the limit
+ *   - the array (73 B per pixel of the limit, 18.3 MiB) is held by every GPU that loads the
+ *     library, until exit; it keeps the previous call's contents (the path clears what must
+ *     start at zero itself)
+ *   - all calls on one device share it: calls that overlap on the GPU (different streams, no
+ *     ordering between them) race.  Calls on one stream, or ordered by events, are safe. */
+#define M3S_MATCH_STATIC_MAX_PIXELS 262144 /* one 512 x 512 pair, or e.g. 4 pairs of 256 x 256 */
+int m3s_match_iterative_proj_static(const float* X11, const float* X21, const float* D11,
+                                    const float* D21, const int32_t* idx_init, int32_t* idx_out,
+                                    uint8_t* valid_out, int B, int H, int W, int D, int max_iter,
+                                    float lambda_init, float convergence_thresh, int radius,
+                                    int dilation_max, float dist_thresh, m3s_stream_t stream);
+
 /* Same computation on HOST arrays (what the reference's caller holds: mast3r_utils.py:490 passes
  * host arrays to matching.match): the batch is cut into chunks of `chunk_pairs` pairs (<= 0: 4)
  * that are uploaded, matched and downloaded on three rotating streams, so the upload of chunk

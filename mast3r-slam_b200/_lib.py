@@ -63,6 +63,8 @@ SIGNATURES = {
     "m3s_match_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "m3s_match_iterative_proj": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f,
                                       _f, _i, _i, _f, _vp, _sz, _vp]),
+    "m3s_match_iterative_proj_static": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i,
+                                             _f, _f, _i, _i, _f, _vp]),
     "m3s_match_iterative_proj_host": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _f,
                                            _f, _i, _i, _f, _i, _i]),
     "m3s_match_host_release": (_i, [_i]),

@@ -126,3 +126,62 @@ M3S_API int m3s_match_iterative_proj(const float* X11, const float* X21, const f
     if (rc) return rc;
     return m3s_match_tail(X11, X21, p1, vproj, idx_out, valid_out, B, H, W, dist_thresh, stream);
 }
+
+// ------------------------------------------------------------------------------------------------
+// m3s_match_iterative_proj_static: the same enqueue with its intermediates in a file-scope device
+// array instead of a caller workspace, for callers that may not allocate (stream capture, serving
+// loops).  No counterpart in the reference.
+//   * limit: B*H*W <= M3S_MATCH_STATIC_MAX_PIXELS (one 512 x 512 pair); the array is 73 B per pixel
+//     + section padding = 18.3 MiB, held by every GPU that loads the library until exit
+//   * no cudaMalloc / cudaFree / allocating library call on this path
+//   * every call on a device shares the array: calls that overlap on the GPU (two streams) race;
+//     what must start at zero (the iter_proj early-exit slots) is cleared by m3s_iter_proj on the
+//     caller's stream at each call, all other sections are written before they are read
+// In host code `g_match_scratch` is only a stand-in for the symbol: its device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+// ------------------------------------------------------------------------------------------------
+static constexpr size_t kStaticMaxPixels = M3S_MATCH_STATIC_MAX_PIXELS;
+static constexpr size_t kStaticScratchBytes = kStaticMaxPixels * 73 + 4096;  // 7 sections, <= 255 B pad each + iter_proj scratch
+static __device__ __align__(256) unsigned char g_match_scratch[kStaticScratchBytes];
+
+static int match_scratch_address(void** out) {
+    static void* cached[64] = {nullptr};  // per device; a benign race writes the same value twice
+    int dev = 0;
+    M3S_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) {
+        set_error("match_iterative_proj_static: device ordinal %d out of range", dev);
+        return M3S_ERR_INVALID;
+    }
+    void* ptr = __atomic_load_n(&cached[dev], __ATOMIC_ACQUIRE);
+    if (!ptr) {
+        M3S_CUDA(cudaGetSymbolAddress(&ptr, g_match_scratch));
+        if (!ptr) {
+            set_error("match_iterative_proj_static: cudaGetSymbolAddress returned a null address");
+            return M3S_ERR_CUDA;
+        }
+        __atomic_store_n(&cached[dev], ptr, __ATOMIC_RELEASE);
+    }
+    *out = ptr;
+    return M3S_OK;
+}
+
+M3S_API int m3s_match_iterative_proj_static(const float* X11, const float* X21, const float* D11,
+                                            const float* D21, const int32_t* idx_init,
+                                            int32_t* idx_out, uint8_t* valid_out, int B, int H, int W,
+                                            int D, int max_iter, float lambda_init,
+                                            float convergence_thresh, int radius, int dilation_max,
+                                            float dist_thresh, m3s_stream_t stream) {
+    M3S_REQUIRE(B >= 0 && H > 0 && W > 0, "match_iterative_proj_static: bad shape");
+    const unsigned long long T = (unsigned long long)B * (unsigned long long)H * (unsigned long long)W;
+    if (T > kStaticMaxPixels || m3s_match_workspace_bytes(B, H, W, max_iter) > kStaticScratchBytes) {
+        set_error("match_iterative_proj_static: B*H*W = %llu pixels exceeds the static scratch limit "
+                  "of %zu (M3S_MATCH_STATIC_MAX_PIXELS); use m3s_match_iterative_proj with a "
+                  "caller workspace", T, kStaticMaxPixels);
+        return M3S_ERR_WORKSPACE;
+    }
+    void* scratch = nullptr;
+    if (int rc = match_scratch_address(&scratch)) return rc;
+    return m3s_match_iterative_proj(X11, X21, D11, D21, idx_init, idx_out, valid_out, B, H, W, D,
+                                    max_iter, lambda_init, convergence_thresh, radius, dilation_max,
+                                    dist_thresh, scratch, kStaticScratchBytes, stream);
+}
