@@ -3544,7 +3544,7 @@ static int tiles_grid_size(m3s_gn_plan* plan) {
 
 // assemble + blocked factorisation of the augmented matrix, enqueued on `st`: one cooperative launch
 // (chol_tiles_kernel, or chol_fused_kernel on request) or, as the fallback, one launch per block step
-static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
+static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st, bool capturing = false) {
     if (int rc = m3s_gn_assemble(plan, reinterpret_cast<m3s_stream_t>(st))) return rc;
     const int np = plan->np;
     const int nblk = np / kNB;
@@ -3560,7 +3560,8 @@ static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
         // the device cannot hold the grid right now (e.g. SMs partitioned away from this context): use the
         // launch-per-step path for this plan from here on -- another CUDA path, never a CPU one
         cudaGetLastError();
-        if (ce != cudaErrorCooperativeLaunchTooLarge && ce != cudaErrorLaunchOutOfResources)
+        // (while capturing, any failure just abandons the graph: the direct launch decides about the path)
+        if (capturing || (ce != cudaErrorCooperativeLaunchTooLarge && ce != cudaErrorLaunchOutOfResources))
             return cuda_fail(ce, "cudaLaunchCooperativeKernel(chol_tiles_kernel)");
         plan->tiles_grid = 0;
     }
@@ -3611,13 +3612,29 @@ static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st) {
 }
 
 // Capture the sequence once on a private stream (so a caller that is itself capturing is not
-// disturbed) and replay it with one cudaGraphLaunch per iteration.
-static void build_solve_graph(m3s_gn_plan* plan) {
+// disturbed) and replay it with one cudaGraphLaunch per iteration: ~90 launches on the
+// launch-per-step path, 5 stream operations incl. the cooperative launch on the dataflow path, whose
+// host-side cost otherwise shows up as gaps on the device when the launching thread is slow (first
+// process on a fresh box: 0.89 instead of 0.54 ms per solve).
+// The zeroing of Hm must not depend on the state at capture time: on the dataflow path (Hm is never
+// written by the factorisation) it is done once here, on the caller's stream, outside the graph; on
+// the in-place paths it is forced into the graph.
+static void build_solve_graph(m3s_gn_plan* plan, cudaStream_t st) {
+    if (tiles_grid_size(plan) > 0) {
+        if (!plan->hm_clean) {
+            if (cudaMemsetAsync(plan->Hm, 0, sizeof(double) * (size_t)(plan->np + 1) * plan->np, st) != cudaSuccess) {
+                plan->graph_failed = true; cudaGetLastError(); return;
+            }
+            plan->hm_clean = true;
+        }
+    } else {
+        plan->hm_clean = false;
+    }
     cudaStream_t cs = nullptr;
     if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess) { plan->graph_failed = true; cudaGetLastError(); return; }
     bool ok = cudaStreamBeginCapture(cs, cudaStreamCaptureModeRelaxed) == cudaSuccess;
     if (ok) {
-        const int rc = enqueue_assemble_factor(plan, cs);
+        const int rc = enqueue_assemble_factor(plan, cs, true);
         cudaGraph_t g = nullptr;
         const cudaError_t e = cudaStreamEndCapture(cs, &g);
         ok = (rc == M3S_OK) && (e == cudaSuccess) && g;
@@ -3640,14 +3657,26 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
     if (plan->F == 0) return M3S_OK;
     cudaStream_t st = as_stream(stream);
     const int np = plan->np;
-    // (the cooperative launch is not captured: the graph only pays off for the ~90 launches of the
-    // launch-per-step path)
-    if (!plan->graph_exec && !plan->graph_failed && np > 2 * kNB && tiles_grid_size(plan) == 0 &&
-        fused_grid_size(plan) == 0)
-        build_solve_graph(plan);
+    // M3S_GN_GRAPH=0 launches directly (A/B, debugging)
+    static const bool use_graph = [] { const char* e = getenv("M3S_GN_GRAPH"); return !(e && e[0] == '0'); }();
+    if (use_graph && !plan->graph_exec && !plan->graph_failed &&
+        (tiles_grid_size(plan) > 0 || (np > 2 * kNB && fused_grid_size(plan) == 0)))
+        build_solve_graph(plan, st);
+    bool launched = false;
     if (plan->graph_exec) {
-        M3S_CUDA(cudaGraphLaunch(plan->graph_exec, st));
-    } else {
+        const cudaError_t ge = cudaGraphLaunch(plan->graph_exec, st);
+        if (ge == cudaSuccess) {
+            launched = true;
+        } else {
+            // e.g. the co-resident grid cannot be placed any more: drop the graph, the direct launch
+            // below picks the path (and reports what it cannot recover from)
+            cudaGetLastError();
+            cudaGraphExecDestroy(plan->graph_exec);
+            plan->graph_exec = nullptr;
+            plan->graph_failed = true;
+        }
+    }
+    if (!launched) {
         if (int rc = enqueue_assemble_factor(plan, st)) return rc;
     }
     // M3S_GN_BACKSOLVE=block: one CTA per 32-column block (round 1); read per call (A/B, tests)
