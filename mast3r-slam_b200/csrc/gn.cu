@@ -747,6 +747,32 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
+// ring reads through 32-bit shared addresses (the stage base is a running register; a generic pointer made
+// ptxas rebuild the shared-window base and the stage offset with ~20 uniform instructions per trip)
+__device__ __forceinline__ float lds_f32(uint32_t a) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ int lds_s32(uint32_t a) {
+    int v;
+    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ unsigned lds_u8(uint32_t a) {
+    unsigned v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+
+// wrapping shared-memory counter: old value, *a = (old >= wrap) ? 0 : old + 1.  (atom.add is turned into a
+// warp-aggregated sequence of 12 instructions by ptxas even when one lane executes it; atom.inc is not, and the
+// counter re-arms itself.)
+__device__ __forceinline__ unsigned atoms_inc_u32(uint32_t a, unsigned wrap) {
+    unsigned old;
+    asm volatile("atom.shared.inc.u32 %0, [%1], %2;" : "=r"(old) : "r"(a), "r"(wrap) : "memory");
+    return old;
+}
 __device__ __forceinline__ void l2_prefetch(const void* src, uint32_t bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
@@ -808,10 +834,9 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
     const long long n1 = min(N, n0 + chunk_pts);
     const int npts = (int)(n1 - n0);                       // multiple of 16
     const int trips = (npts + Cfg::kPts - 1) / Cfg::kPts;
-    const uint32_t ring_s = smem_u32(ring), bars_s = smem_u32(bars);
+    const uint32_t ring_s = smem_u32(ring), bars_s = smem_u32(bars), cnt_s = smem_u32(stage_cnt);
 
-    auto issue = [&](int trip) {  // thread 0: arm the stage barrier and start its five copies
-        const int st = trip % STAGES;
+    auto issue = [&](int trip, int st) {  // one thread: arm the barrier of stage st (= trip % STAGES) and start its five copies
         const long long g0 = n0 + (long long)trip * Cfg::kPts;
         const uint32_t cnt = (uint32_t)min((long long)Cfg::kPts, n1 - g0);
         const uint32_t bar = bars_s + 8u * st, base = ring_s + (uint32_t)st * Cfg::kStageBytes;
@@ -835,7 +860,7 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
         for (int k = 0; k < STAGES; ++k) mbar_init(bars_s + 8u * k, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        for (int k = 0; k < STAGES && k < trips; ++k) issue(k);
+        for (int k = 0; k < STAGES && k < trips; ++k) issue(k, k);
         // sim3_relative (sim3_ops.py:96-126) in fp64, then split (as gn_accum_mixed_kernel)
         const double* Ti = poses + 8 * em.ix;
         const double* Tj = poses + 8 * em.jx;
@@ -868,6 +893,16 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
     __syncthreads();
     const EdgeConstF ec = ec_s;
     const int Ni = (int)N;
+    // gather bases held as register pairs (one IMAD.WIDE per address; ptxas otherwise re-derives
+    // Xs + 3 N ix + 3 m from the kernel parameters in 64-bit pieces for every point: 3-4 instructions each)
+    const float* Xi_r = Xi;
+    const float* Ci_r = Ci;
+    asm volatile("" : "+l"(Xi_r));
+    asm volatile("" : "+l"(Ci_r));
+    // fetches run in trip order: stage, wait parity and the points left are running values (no trip % STAGES)
+    const int j0 = (tid >> 5) * 128 + (tid & 31);
+    uint32_t f_st = 0, f_par = 0;
+    int f_lim = npts - j0;
 
     float2 acc2[NA];
 #pragma unroll
@@ -880,52 +915,48 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
         float ci[4], xi[4][3];
         bool ok[4];
     };
-    auto release = [&](int trip) {
+    auto release = [&](int trip, int st) {
         // Stage hand-back without anybody waiting: every warp counts itself out of the stage
         // (shared-memory atomic, ordered behind its ring reads in the LSU queue); the LAST warp to
         // leave re-arms the stage.  (A fixed producer warp that bar.sync'ed on the others spent half
         // of its time in that barrier: ncu s17, 12.6 % of all stall samples.)
-        const int st = trip % STAGES;
         __syncwarp();
         if ((tid & 31) == 0) {
-            const unsigned int old = atomicAdd(&stage_cnt[st], 1u);
+            const unsigned int old = atoms_inc_u32(cnt_s + 4u * (uint32_t)st, TPB / 32 - 1);
             if (old == TPB / 32 - 1) {
-                stage_cnt[st] = 0u;
-                if (trip + STAGES < trips) issue(trip + STAGES);
+                if (trip + STAGES < trips) issue(trip + STAGES, st);
             }
         }
     };
     // wait for the stage, pull this thread's 4 points into registers, release the stage, start the
     // (Ci, Xi) gathers.  Returns with the gathers in flight.
     auto fetch = [&](int trip, Trip& T) {
-        const int st = trip % STAGES;
-        mbar_wait(bars_s + 8u * st, (uint32_t)((trip / STAGES) & 1));
-        const unsigned char* base = ring + (size_t)st * Cfg::kStageBytes;
+        const int st = (int)f_st;
+        mbar_wait(bars_s + 8u * f_st, f_par);
+        const uint32_t sb = ring_s + f_st * (uint32_t)Cfg::kStageBytes;
         // Lane l of warp w takes points w*128 + l + 32*u (u = 0..3) of the stage: for a fixed u the
         // warp's 32 points are CONSECUTIVE, so with idx ~ identity + flow the (Ci, Xi) gathers of one
         // LDG touch 1-2 / 3-4 cache lines instead of 4 / 12 when a thread owns 4 adjacent points
         // (the L1 tag stage, one line per clock, was the limiter of the register-staged kernels).
         // The shared-memory reads are conflict-free either way (word stride 1, or 3 for Xj).
-        const int j0 = (tid >> 5) * 128 + (tid & 31);
-        unsigned char vv[4];
+        const uint32_t a1 = sb + (uint32_t)j0, a4 = sb + 4u * (uint32_t)j0, a12 = sb + 12u * (uint32_t)j0;
+        unsigned vv[4];
         int ii4[4];
         float cc[4], qg[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            const int j = j0 + 32 * u;
             // points past the end of a partial last stage read stale ring bytes: harmless, the gate
             // below fails on `in` and a failed point is neutralised before any arithmetic
-            const bool in = (trip * Cfg::kPts + j) < npts;
-            vv[u] = in ? base[Cfg::kOffV + j] : (unsigned char)0;
-            qg[u] = reinterpret_cast<const float*>(base + Cfg::kOffQ)[j];
-            ii4[u] = reinterpret_cast<const int*>(base + Cfg::kOffI)[j];
-            cc[u] = reinterpret_cast<const float*>(base + Cfg::kOffC)[j];
+            const bool in = 32 * u < f_lim;
+            vv[u] = in ? lds_u8(a1 + Cfg::kOffV + 32 * u) : 0u;
+            qg[u] = lds_f32(a4 + Cfg::kOffQ + 128 * u);
+            ii4[u] = lds_s32(a4 + Cfg::kOffI + 128 * u);
+            cc[u] = lds_f32(a4 + Cfg::kOffC + 128 * u);
             if constexpr (!kSlim) {
-                const float* xp = reinterpret_cast<const float*>(base + Cfg::kOffX) + 3 * j;
                 T.qq[u] = qg[u];
-                T.xj[u][0] = xp[0];
-                T.xj[u][1] = xp[1];
-                T.xj[u][2] = xp[2];
+                T.xj[u][0] = lds_f32(a12 + Cfg::kOffX + 384 * u);
+                T.xj[u][1] = lds_f32(a12 + Cfg::kOffX + 384 * u + 4);
+                T.xj[u][2] = lds_f32(a12 + Cfg::kOffX + 384 * u + 8);
             }
         }
 #pragma unroll
@@ -934,12 +965,14 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
             m += (m < 0) ? Ni : 0;  // numpy negative indexing (gauss_newton.py:125)
             T.ok[u] = vv[u] && ((unsigned)m < (unsigned)Ni) && (qg[u] > P.q_th) && (cc[u] > P.c_th);
             m = T.ok[u] ? m : 0;
-            T.ci[u] = __ldg(Ci + m);
-            const float* __restrict__ xp = Xi + 3 * (size_t)(unsigned)m;
+            T.ci[u] = __ldg(Ci_r + (unsigned)m);
+            const float* __restrict__ xp = Xi_r + 3 * (size_t)(unsigned)m;
             T.xi[u][0] = __ldg(xp); T.xi[u][1] = __ldg(xp + 1); T.xi[u][2] = __ldg(xp + 2);
         }
         // (placed after the gate, which consumes the shared-memory loads: they have landed)
-        if constexpr (!kSlim) release(trip);
+        if constexpr (!kSlim) release(trip, st);
+        if (++f_st == (uint32_t)STAGES) { f_st = 0; f_par ^= 1u; }
+        f_lim -= Cfg::kPts;
     };
     auto compute = [&](int trip, const Trip& T) {
         bool okf[4];
@@ -948,7 +981,6 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
         float xj[4][3], qq[4];
         if constexpr (kSlim) {
             const unsigned char* base = ring + (size_t)(trip % STAGES) * Cfg::kStageBytes;
-            const int j0 = (tid >> 5) * 128 + (tid & 31);
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const int j = j0 + 32 * u;
@@ -965,6 +997,20 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
         }
 #ifdef M3S_ACCS_DUAL   // both pairs in one basic block (more ILP, 168 registers): measured 1.267 vs 1.257 ms
         const bool any4 = okf[0] | okf[1] | okf[2] | okf[3];
+#endif
+#ifdef M3S_ACCS_FASTPATH
+        // every point of the warp's trip passes the gate (the common case): the same arithmetic on the raw
+        // values, without the 14 selects per pair that neutralise a gated-out point (bit-identical).  Measured
+        // SLOWER (1.176 vs 1.150 ms): the selects ride on the ALU pipe beside the packed FMA work, the vote and
+        // the duplicated code do not
+        if (__all_sync(0xffffffffu, okf[0] & okf[1] & okf[2] & okf[3])) {
+#pragma unroll
+            for (int u = 0; u < 4; u += 2)
+                accumulate_pair_f32<MODE>(P, ec, make_float2(xj[u][0], xj[u + 1][0]), make_float2(xj[u][1], xj[u + 1][1]),
+                                          make_float2(xj[u][2], xj[u + 1][2]), make_float2(T.xi[u][0], T.xi[u + 1][0]),
+                                          make_float2(T.xi[u][1], T.xi[u + 1][1]), make_float2(T.xi[u][2], T.xi[u + 1][2]),
+                                          make_float2(qq[u], qq[u + 1]), acc2);
+        } else
 #endif
 #pragma unroll
         for (int u = 0; u < 4; u += 2) {
@@ -985,7 +1031,7 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
                     make_float2(a ? qq[u] : 0.f, b ? qq[u + 1] : 0.f), acc2);
             }
         }
-        if constexpr (kSlim) release(trip);   // the arithmetic above consumed the ring reads
+        if constexpr (kSlim) release(trip, trip % STAGES);   // the arithmetic above consumed the ring reads
     };
 
     if (trips > 0) {
