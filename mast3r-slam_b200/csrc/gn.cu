@@ -846,6 +846,10 @@ gn_accum_stream_kernel(const Status* __restrict__ status, KernelParams P,
         bulk_g2s(base + Cfg::kOffI, ide + g0, cnt * 4u, bar);
         bulk_g2s(base + Cfg::kOffC, Cj + g0, cnt * 4u, bar);
         bulk_g2s(base + Cfg::kOffV, ve + g0, cnt, bar);
+#ifdef M3S_ACCS_GPF    // L2 prefetch of the gather targets assuming idx ~ identity + flow: measured SLOWER (1.208 vs 1.149 ms)
+        l2_prefetch(Xi + 3 * g0, cnt * 12u);
+        l2_prefetch(Ci + g0, cnt * 4u);
+#endif
 #ifdef M3S_ACCS_L2PF   // L2 prefetch of the stage M3S_ACCS_L2PF trips further on: measured SLOWER (8: 1.246, 16: 1.251 vs 1.201 ms)
         const long long gp = g0 + (long long)M3S_ACCS_L2PF * Cfg::kPts;
         if (gp < n1) {
