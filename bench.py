@@ -660,6 +660,7 @@ def gn_leg(args, rank, world, dev, peak, precision, check=True):
     err0 = float(abs(g["Twc"] - g["Twc_gt"]).max())
     exchange = sg.exchange
     solve_path = int(lib.m3s_gn_plan_factor_path(sg.plan.handle))
+    sparse_info = sg.plan.sparse_info()
     sg.close()
     out = {
         "metric": "gn_iters_per_s (gauss_newton_points, 200 KF / 1000 directed edges, 196608 pts/KF)",
@@ -670,7 +671,9 @@ def gn_leg(args, rank, world, dev, peak, precision, check=True):
         "edges_this_rank": ne, "dim": sg.plan.dim,
         "accumulate_ms": round(acc_ms, 4), "solve_update_ms": round(ms - acc_ms, 4),
         "solve_path": {0: "steps (one launch per block step)", 1: "fused (persistent chain + workers)",
-                       2: "tiles (dataflow over shared-memory-resident tiles)"}[solve_path],
+                       2: "tiles (dataflow over shared-memory-resident tiles)",
+                       3: "sparse front (levels of exactly eliminated keyframes) + tiles on the dense tail"}[solve_path],
+        "sparse_front": sparse_info,
         "precision": precision, "_poses": poses_after.cpu(),
         "roofline": {"bound": "hbm",
                      "kernel": "gn_accum_stream_kernel" if precision == "mixed" else "gn_accum_kernel",

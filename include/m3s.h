@@ -247,8 +247,16 @@ int m3s_gn_plan_dim(const m3s_gn_plan* plan);           /* 7 F */
 int m3s_gn_plan_ld(const m3s_gn_plan* plan);            /* row stride of H: dim rounded up to 32 */
 /* factorisation path m3s_gn_solve_update will take for this plan on the current device:
  * 0 = one launch per block step, 1 = persistent chain + workers (M3S_GN_CHOL=fused),
- * 2 = dataflow over shared-memory-resident tiles (default when every tile CTA is co-resident) */
+ * 2 = dataflow over shared-memory-resident tiles (default when every tile CTA is co-resident),
+ * 3 = sparse front (keyframes with few neighbours eliminated exactly as 7x7 blocks, level by level) +
+ *     path 2 on the Schur complement of the remaining keyframes (default when the graph is sparse
+ *     enough to shorten the dense chain; M3S_GN_SPARSE=0 or M3S_GN_CHOL=steps|fused|tiles keep it dense).
+ * Same system as gauss_newton.py:254-265 (H + 1e-6 I, Cholesky); only the elimination order differs. */
 int m3s_gn_plan_factor_path(m3s_gn_plan* plan);
+/* sparse front of the plan: out[0] = levels (0 = not used), out[1] = keyframes eliminated in the levels,
+ * out[2] = keyframes of the dense tail, out[3] = padded dimension of the tail system.  Diagnostic; no
+ * counterpart in the reference (its solve is one dense Cholesky, gauss_newton.py:254-262). */
+int m3s_gn_plan_sparse_info(const m3s_gn_plan* plan, int32_t* out);
 /* device pointer + element count of the packed per-edge blocks [E][M3S_GN_EDGE_STRIDE] f64 that
  * m3s_gn_accumulate writes and m3s_gn_solve_update reads: the buffer a multi-GPU caller
  * all-reduces (sum) between the two when edges are sharded across ranks. */

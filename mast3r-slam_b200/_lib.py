@@ -80,6 +80,7 @@ SIGNATURES = {
     "m3s_gn_plan_dim": (_i, [_vp]),
     "m3s_gn_plan_ld": (_i, [_vp]),
     "m3s_gn_plan_factor_path": (_i, [_vp]),
+    "m3s_gn_plan_sparse_info": (_i, [_vp, _vp]),
     "m3s_gn_plan_edge_blocks": (_vp, [_vp, C.POINTER(_i64)]),
     "m3s_gn_plan_H": (_vp, [_vp]),
     "m3s_gn_plan_g": (_vp, [_vp]),

@@ -18,6 +18,7 @@
 #include <algorithm>
 #include <map>
 #include <new>
+#include <set>
 #include <utility>
 #include <vector>
 
@@ -2842,7 +2843,7 @@ gn_backsolve_group_kernel(Status* __restrict__ status, const double* __restrict_
                           const int* __restrict__ free_kf, double delta_thresh,
                           double* __restrict__ xsol, int* __restrict__ flags, int epoch,
                           double* __restrict__ dx_out, double* __restrict__ poses,
-                          long long* __restrict__ tl, int metal) {
+                          long long* __restrict__ tl, int metal, int finish) {
     if (status->stopped | status->failed) return;
     const int nblk = np / kNB;
     const int gi = blockIdx.x;
@@ -2945,7 +2946,7 @@ gn_backsolve_group_kernel(Status* __restrict__ status, const double* __restrict_
     }
     __syncthreads();
     if (tid == 0) { __threadfence(); st_release(flags + gi, epoch); tl_stamp(tl, (3 * nblk + b_lo) * 2 + 1); }
-    if (b_lo != 0) return;
+    if (b_lo != 0 || !finish) return;   // finish == 0: the sparse-front kernels complete and apply the step
 
     // ---- block 0: all of x is published (x_0 depended on every other block) ----------------------
     __shared__ double red[kBackThreads / 32];
@@ -2983,6 +2984,267 @@ gn_backsolve_group_kernel(Status* __restrict__ status, const double* __restrict_
         double xi[7];
 #pragma unroll
         for (int k = 0; k < 7; ++k) xi[k] = __ldcg(xsol + 7 * f + k);
+        if (metal) sim3_retract_metal_dev(xi, poses + 8 * free_kf[f]);
+        else sim3_retract_dev(xi, poses + 8 * free_kf[f]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Sparse front (default when the pose graph leaves H sparse enough, M3S_GN_SPARSE=0 disables): keyframes
+// that are mutually non-adjacent and have few neighbours are eliminated EXACTLY as 7x7 blocks, level by
+// level (each level = an independent set of the graph that the previous levels left, fill included), and
+// only the Schur complement on the remaining keyframes -- the "tail" -- goes through the dense blocked
+// factorisation above.  For the window-2 chain + loop closures of config 5 (199 free keyframes) ~150
+// keyframes leave in 7 levels and the dense chain shrinks from 22 tiles to 6.
+//   level kernel (left-looking, one CTA per keyframe j of the level):
+//     A~_aj = H_aj - sum_i W_ai W_ji^T   over the earlier-eliminated i with a, j in struct(i)   (a in {j} + struct(j))
+//     b~_j  = -g_j - sum_i W_ji y_i
+//     G = chol(A~_jj),  W_aj = A~_aj G^-T,  y_j = G^-1 b~_j         (W, G^-1, y kept for the back-substitution)
+//   tail kernel: Hr_ab = H_ab - sum_i W_ai W_bi^T,  rhs_a = -g_a - sum_i W_ai y_i   (dense, tail order)
+//   after the dense solve of the tail, the levels in reverse:  x_j = G^-T (y_j - sum_a W_aj^T x_a).
+// Every sum runs over a host-built list in a fixed order: no atomics, bitwise reproducible, identical on every
+// rank.  H (Hm) is only read.
+// ------------------------------------------------------------------------------------------------
+constexpr int kSpMaxRows = 25;      // 1 + the largest struct a level keyframe may have
+constexpr int kSpThreads = 256;     // 4 groups of 64 (49 active) -- one 7x7 block per group at a time
+
+struct SpDev {
+    const int* enode;      // [nE] free index of the eliminated keyframes, level-major
+    const int* row_ptr;    // [nE + 1] rows of keyframe e: row 0 = itself, then struct(e)
+    const int* row_node;   // [nrows] free index of the row's keyframe
+    const int* con_ptr;    // [nrows + 1] contributor pairs of the row
+    const int2* con;       // (W slot of (a, i), W slot of (j, i))
+    const int* rc_ptr;     // [nE + 1] right-hand-side contributors of keyframe e
+    const int2* rc;        // (W slot of (j, i), e index of i)
+    double* W;             // [nrows][49]; the slot of row (e, s) is its row index (row 0 slots unused)
+    double* Ginv;          // [nE][49]
+    double* y;             // [nE][7]
+};
+
+__global__ void __launch_bounds__(kSpThreads)
+sp_level_kernel(Status* __restrict__ status, SpDev sp, int e_begin, const double* __restrict__ Hm, int np) {
+    if (status->stopped | status->failed) return;
+    __shared__ double At[kSpMaxRows][49];
+    __shared__ double Gi[49];
+    __shared__ double bt[7];
+    const int e = e_begin + blockIdx.x;
+    const int j = sp.enode[e];
+    const int r0 = sp.row_ptr[e], nrows = sp.row_ptr[e + 1] - r0;
+    const int tid = threadIdx.x, grp = tid >> 6, t = tid & 63;
+    const int r = t / 7, c = t % 7;
+    for (int s = grp; s < nrows; s += kSpThreads / 64) {
+        if (t < 49) {
+            const int a = sp.row_node[r0 + s];
+            double acc = Hm[(size_t)(7 * a + r) * np + 7 * j + c];
+            for (int q = sp.con_ptr[r0 + s]; q < sp.con_ptr[r0 + s + 1]; ++q) {
+                const int2 w = sp.con[q];
+                const double* wa = sp.W + (size_t)w.x * 49 + r * 7;
+                const double* wj = sp.W + (size_t)w.y * 49 + c * 7;
+                double d = 0.0;
+#pragma unroll
+                for (int k = 0; k < 7; ++k) d = fma(wa[k], wj[k], d);
+                acc -= d;
+            }
+            At[s][t] = acc;
+        } else if (s == 0 && t < 56) {
+            const int rr = t - 49;
+            double acc = Hm[(size_t)np * np + 7 * j + rr];
+            for (int q = sp.rc_ptr[e]; q < sp.rc_ptr[e + 1]; ++q) {
+                const int2 w = sp.rc[q];
+                const double* wj = sp.W + (size_t)w.x * 49 + rr * 7;
+                const double* yi = sp.y + (size_t)w.y * 7;
+                double d = 0.0;
+#pragma unroll
+                for (int k = 0; k < 7; ++k) d = fma(wj[k], yi[k], d);
+                acc -= d;
+            }
+            bt[rr] = acc;
+        }
+    }
+    __syncthreads();
+    if (tid < 7) {   // column tid of G^-1 after thread 0's Cholesky: 7x7, latency only
+        if (tid == 0) {
+            bool bad = false;
+            for (int k = 0; k < 7; ++k) {
+                double d = At[0][k * 7 + k];
+                for (int m = 0; m < k; ++m) d -= At[0][k * 7 + m] * At[0][k * 7 + m];
+                if (!(d > 0.0)) { bad = true; d = 1.0; }
+                const double g = sqrt(d), gi = 1.0 / g;
+                At[0][k * 7 + k] = g;
+                for (int i = k + 1; i < 7; ++i) {
+                    double v = At[0][i * 7 + k];
+                    for (int m = 0; m < k; ++m) v -= At[0][i * 7 + m] * At[0][k * 7 + m];
+                    At[0][i * 7 + k] = v * gi;
+                }
+            }
+            if (bad) status->chol_fail = 1;
+        }
+        __syncwarp(0x7fu);
+        double x[7];
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {   // G x = e_tid
+            double v = (i == tid) ? 1.0 : 0.0;
+#pragma unroll
+            for (int m = 0; m < 7; ++m)
+                if (m < i) v -= At[0][i * 7 + m] * x[m];
+            x[i] = v / At[0][i * 7 + i];
+        }
+#pragma unroll
+        for (int i = 0; i < 7; ++i) Gi[i * 7 + tid] = x[i];
+    }
+    __syncthreads();
+    for (int s = 1 + grp; s < nrows; s += kSpThreads / 64) {
+        if (t < 49) {   // W_aj = A~_aj G^-T
+            double d = 0.0;
+#pragma unroll
+            for (int k = 0; k < 7; ++k) d = fma(At[s][r * 7 + k], Gi[c * 7 + k], d);
+            sp.W[(size_t)(r0 + s) * 49 + t] = d;
+        }
+    }
+    if (tid < 49) sp.Ginv[(size_t)e * 49 + tid] = Gi[tid];
+    if (tid >= 64 && tid < 71) {
+        const int rr = tid - 64;
+        double d = 0.0;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) d = fma(Gi[rr * 7 + k], bt[k], d);
+        sp.y[(size_t)e * 7 + rr] = d;
+    }
+}
+
+// Schur complement on the tail, written as the dense augmented matrix the blocked factorisation reads
+// (row-major [npR + 1][npR], both triangles, rhs in row npR; padding = identity, set once at plan creation).
+struct SpTailDev {
+    const int* rnode;      // [nR] free index of tail keyframe
+    const int2* blk;       // [nblk] (ra, rb), ra >= rb, tail indices
+    const int* con_ptr;    // [nblk + 1]
+    const int2* con;       // (W slot of (a, i), W slot of (b, i))
+    const int* rc_ptr;     // [nR + 1]
+    const int2* rc;        // (W slot of (a, i), e index of i)
+};
+
+__global__ void __launch_bounds__(64)
+sp_tail_kernel(const Status* __restrict__ status, SpDev sp, SpTailDev tl, const double* __restrict__ Hm, int np,
+               double* __restrict__ Hr, int npR) {
+    if (status->stopped | status->failed) return;
+    const int2 rb = tl.blk[blockIdx.x];
+    const int a = tl.rnode[rb.x], b = tl.rnode[rb.y];
+    const int t = threadIdx.x;
+    if (t < 49) {
+        const int r = t / 7, c = t % 7;
+        double acc = Hm[(size_t)(7 * a + r) * np + 7 * b + c];
+        for (int q = tl.con_ptr[blockIdx.x]; q < tl.con_ptr[blockIdx.x + 1]; ++q) {
+            const int2 w = tl.con[q];
+            const double* wa = sp.W + (size_t)w.x * 49 + r * 7;
+            const double* wb = sp.W + (size_t)w.y * 49 + c * 7;
+            double d = 0.0;
+#pragma unroll
+            for (int k = 0; k < 7; ++k) d = fma(wa[k], wb[k], d);
+            acc -= d;
+        }
+        Hr[(size_t)(7 * rb.x + r) * npR + 7 * rb.y + c] = acc;
+        if (rb.x != rb.y) Hr[(size_t)(7 * rb.y + c) * npR + 7 * rb.x + r] = acc;
+    } else if (rb.x == rb.y && t < 56) {
+        const int rr = t - 49;
+        double acc = Hm[(size_t)np * np + 7 * a + rr];
+        for (int q = tl.rc_ptr[rb.x]; q < tl.rc_ptr[rb.x + 1]; ++q) {
+            const int2 w = tl.rc[q];
+            const double* wa = sp.W + (size_t)w.x * 49 + rr * 7;
+            const double* yi = sp.y + (size_t)w.y * 7;
+            double d = 0.0;
+#pragma unroll
+            for (int k = 0; k < 7; ++k) d = fma(wa[k], yi[k], d);
+            acc -= d;
+        }
+        Hr[(size_t)npR * npR + 7 * rb.x + rr] = acc;
+    }
+}
+
+// x of the tail (dense back-substitution result, tail order) into the natural-order step vector
+__global__ void sp_scatter_tail_kernel(const Status* __restrict__ status, const int* __restrict__ rnode, int nR,
+                                       const double* __restrict__ xsol, double* __restrict__ dx) {
+    if (status->stopped | status->failed) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 7 * nR) dx[7 * rnode[i / 7] + i % 7] = xsol[i];
+}
+
+// one level of the back-substitution: x_j = G^-T (y_j - sum_a W_aj^T x_a), one 64-thread CTA per keyframe
+__global__ void __launch_bounds__(64)
+sp_back_kernel(const Status* __restrict__ status, SpDev sp, int e_begin, double* __restrict__ dx) {
+    if (status->stopped | status->failed) return;
+    __shared__ double part[8][7];
+    __shared__ double tv[7];
+    const int e = e_begin + blockIdx.x;
+    const int r0 = sp.row_ptr[e], nrows = sp.row_ptr[e + 1] - r0;
+    const int t = threadIdx.x;
+    if (t < 56) {
+        const int k = t % 7, p = t / 7;   // partial p of component k: rows s = 1 + p, 9 + p, ...
+        double acc = 0.0;
+        for (int s = 1 + p; s < nrows; s += 8) {
+            const double* w = sp.W + (size_t)(r0 + s) * 49 + k;
+            const double* xa = dx + 7 * sp.row_node[r0 + s];
+#pragma unroll
+            for (int r = 0; r < 7; ++r) acc = fma(w[r * 7], xa[r], acc);
+        }
+        part[p][k] = acc;
+    }
+    __syncthreads();
+    if (t < 7) {
+        double v = sp.y[(size_t)e * 7 + t];
+#pragma unroll
+        for (int p = 0; p < 8; ++p) v -= part[p][t];
+        tv[t] = v;
+    }
+    __syncthreads();
+    if (t < 7) {
+        const double* gi = sp.Ginv + (size_t)e * 49;
+        double d = 0.0;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) d = fma(gi[k * 7 + t], tv[k], d);
+        dx[7 * sp.enode[e] + t] = d;
+    }
+}
+
+// ||dx|| test before applying (gauss_newton.py:263-265) and the Sim3 retraction, as the tail of the dense
+// back-substitution kernels, for the sparse-front path (dx is complete in natural order)
+__global__ void __launch_bounds__(kBackThreads)
+sp_finish_kernel(Status* __restrict__ status, const double* __restrict__ dx, int dim, int num_free,
+                 const int* __restrict__ free_kf, double delta_thresh, double* __restrict__ poses, int metal) {
+    if (status->stopped | status->failed) return;
+    const int tid = threadIdx.x;
+    __shared__ double red[kBackThreads / 32];
+    __shared__ int decision;  // 0 apply, 1 stop, 2 fail
+    double psum = 0.0;
+    int nonfinite = 0;
+    for (int i = tid; i < dim; i += kBackThreads) {
+        const double v = dx[i];
+        psum += v * v;
+        if (!(fabs(v) <= 1.7e308)) nonfinite = 1;
+    }
+    psum = warp_sum(psum);
+    nonfinite = __any_sync(0xffffffffu, nonfinite);
+    if ((tid & 31) == 0) red[tid >> 5] = nonfinite ? __longlong_as_double(0x7ff8000000000000LL) : psum;
+    __syncthreads();
+    if (tid == 0) {
+        double s = 0.0;
+        for (int w = 0; w < kBackThreads / 32; ++w) s += red[w];
+        const double nrm = sqrt(s);
+        status->last_norm = nrm;
+        status->attempted += 1;
+        int d;
+        if (!(nrm == nrm)) d = 2;
+        else if (nrm < delta_thresh) d = 1;
+        else d = 0;
+        if (d == 1) status->stopped = 1;
+        if (d == 2) status->failed = 1;
+        if (d == 0) status->applied += 1;
+        decision = d;
+    }
+    __syncthreads();
+    if (decision != 0) return;
+    for (int f = tid; f < num_free; f += kBackThreads) {
+        double xi[7];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) xi[k] = dx[7 * f + k];
         if (metal) sim3_retract_metal_dev(xi, poses + 8 * free_kf[f]);
         else sim3_retract_dev(xi, poses + 8 * free_kf[f]);
     }
@@ -3040,6 +3302,15 @@ struct m3s_gn_plan {
     unsigned* tctl = nullptr;       // flag words of the dataflow factorisation (chol_tiles_kernel)
     int tiles_grid = -1;            // its CTA count (0 = not available / not selected, -1 = not probed)
     long long* timeline = nullptr;  // [4, np / 32, 2] globaltimer stamps (M3S_GN_TIMELINE=1), else null
+    // sparse front (sp_level_kernel ...): levels of exactly eliminated keyframes + a dense tail
+    bool sp_on = false;
+    int sp_nE = 0, sp_nR = 0, sp_dimR = 0, sp_npR = 0, sp_ntail_blocks = 0;
+    std::vector<int> sp_level_begin;   // [levels + 1] into the level-major list of eliminated keyframes
+    SpDev sp{};
+    SpTailDev spt{};
+    double* sp_Hr = nullptr;           // [npR + 1, npR] Schur complement on the tail (+ rhs row)
+    int sp_tiles_grid = 0;             // CTAs of chol_tiles_kernel for the tail
+    std::vector<void*> sp_allocs;
     double* g = nullptr;            // [dim]
     double* dx = nullptr;           // [dim]
     Status* status = nullptr;
@@ -3086,9 +3357,16 @@ static void xch_free(m3s_gn_plan* p) {
     cudaGetLastError();
 }
 
+static void plan_free(m3s_gn_plan* p);
+static void sp_free(m3s_gn_plan* p) {
+    for (void* q : p->sp_allocs) cudaFree(q);
+    p->sp_allocs.clear();
+    p->sp_on = false;
+}
 static void plan_free(m3s_gn_plan* p) {
     if (!p) return;
     xch_free(p);
+    sp_free(p);
     if (p->graph_exec) cudaGraphExecDestroy(p->graph_exec);
     if (p->graph) cudaGraphDestroy(p->graph);
     cudaFree(p->Lm); cudaFree(p->xsol); cudaFree(p->flags); cudaFree(p->gbar); cudaFree(p->tctl); cudaFree(p->timeline);
@@ -3104,6 +3382,168 @@ static bool dev_alloc_copy(T** dst, const std::vector<T>& src) {
     if (cudaMalloc(reinterpret_cast<void**>(dst), bytes) != cudaSuccess) return false;
     if (!src.empty() && cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess)
         return false;
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Sparse front, host side: symbolic elimination on the keyframe graph at plan creation.
+// Level l = a greedy independent set (lowest current degree first) of the keyframes with at most
+// kSpMaxRows - 1 neighbours in the graph the earlier levels left (fill edges included).  Levels are added
+// while one is worth its two launches (>= kSpMinLevel keyframes ~ 2/3 of a 64-row tile of the dense chain).
+// Selected by default when it removes at least one tile from the dense chain; M3S_GN_SPARSE=0 or an
+// explicit M3S_GN_CHOL=steps|fused|tiles keeps the whole system dense, M3S_GN_CHOL=sparse forces it.
+// ------------------------------------------------------------------------------------------------
+constexpr int kSpMinLevel = 6;
+constexpr int kSpMaxLevels = 12;
+
+template <typename T>
+static bool sp_upload(m3s_gn_plan* p, const T** dst, const std::vector<T>& src) {
+    T* d = nullptr;
+    const size_t n = std::max<size_t>(src.size(), 1);
+    if (cudaMalloc((void**)&d, sizeof(T) * n) != cudaSuccess) return false;
+    p->sp_allocs.push_back(d);
+    if (!src.empty() && cudaMemcpy(d, src.data(), sizeof(T) * src.size(), cudaMemcpyHostToDevice) != cudaSuccess) return false;
+    *dst = d;
+    return true;
+}
+
+static bool sp_env_allows(bool* forced) {
+    *forced = false;
+    if (const char* e = getenv("M3S_GN_SPARSE")) if (e[0] == '0') return false;
+    if (const char* e = getenv("M3S_GN_CHOL")) {
+        if (strcmp(e, "sparse") == 0) { *forced = true; return true; }
+        if (e[0] != 0) return false;   // steps | fused | tiles: the dense paths
+    }
+    return true;
+}
+
+// off_pairs: the structurally non-zero off-diagonal blocks (hi, lo) of H in free-keyframe indices
+static bool build_sparse_front(m3s_gn_plan* p, const std::vector<std::pair<int, int>>& off_pairs) {
+    bool forced = false;
+    const int F = p->F;
+    if (!sp_env_allows(&forced) || F < 2) return true;
+    std::vector<std::set<int>> adj(F);
+    for (auto& pr : off_pairs) { adj[pr.first].insert(pr.second); adj[pr.second].insert(pr.first); }
+    std::vector<char> alive(F, 1);
+    std::vector<std::vector<int>> strct(F);
+    std::vector<int> elim_pos(F, -1);        // e index (level-major) of an eliminated keyframe
+    std::vector<int> enode, level_begin{0};
+    int n_alive = F;
+    for (int l = 0; l < kSpMaxLevels; ++l) {
+        std::vector<std::pair<int, int>> cand;
+        for (int v = 0; v < F; ++v)
+            if (alive[v] && (int)adj[v].size() <= kSpMaxRows - 1) cand.push_back({(int)adj[v].size(), v});
+        std::sort(cand.begin(), cand.end());
+        std::vector<char> blocked(F, 0);
+        std::vector<int> sel;
+        for (auto& dv : cand) {
+            const int v = dv.second;
+            if (blocked[v] || (int)sel.size() >= n_alive - 1) continue;   // the tail keeps >= 1 keyframe
+            sel.push_back(v);
+            blocked[v] = 1;
+            for (int n : adj[v]) blocked[n] = 1;
+        }
+        if ((int)sel.size() < (forced ? 1 : kSpMinLevel)) break;
+        std::sort(sel.begin(), sel.end());
+        for (int v : sel) {
+            strct[v].assign(adj[v].begin(), adj[v].end());
+            for (int a : strct[v]) {
+                adj[a].erase(v);
+                for (int b : strct[v]) if (b != a) adj[a].insert(b);
+            }
+            adj[v].clear();
+            alive[v] = 0;
+            elim_pos[v] = (int)enode.size();
+            enode.push_back(v);
+            --n_alive;
+        }
+        level_begin.push_back((int)enode.size());
+    }
+    const int nE = (int)enode.size(), nR = F - nE;
+    if (nE == 0) return true;
+    const int dimR = 7 * nR, npR = ((dimR + kNB - 1) / kNB) * kNB;
+    const int nt_full = (p->np + kTS - 1) / kTS, nt_tail = (npR + kTS - 1) / kTS;
+    if (!forced && nt_tail >= nt_full) return true;   // nothing to win
+    // rows, W slots (slot = global row index), contributor lists
+    std::vector<int> row_ptr{0}, row_node, con_ptr{0}, rc_ptr{0};
+    std::vector<int2> con, rc;
+    std::map<std::pair<int, int>, int> wslot;   // (a, i) -> row index of a in keyframe i's rows
+    for (int e = 0; e < nE; ++e) {
+        const int j = enode[e];
+        row_node.push_back(j);
+        for (int a : strct[j]) { wslot[{a, j}] = (int)row_node.size(); row_node.push_back(a); }
+        row_ptr.push_back((int)row_node.size());
+    }
+    // contributors of keyframe v: the earlier-eliminated i with v in struct(i), in elimination order
+    std::vector<std::vector<int>> contrib_of(F);
+    for (int e = 0; e < nE; ++e)
+        for (int a : strct[enode[e]]) contrib_of[a].push_back(e);
+    for (int e = 0; e < nE; ++e) {
+        const int j = enode[e];
+        for (int r = row_ptr[e]; r < row_ptr[e + 1]; ++r) {
+            const int a = row_node[r];
+            for (int ei : contrib_of[j]) {           // ei < e by construction (j was alive when ei left)
+                const int i = enode[ei];
+                auto ia = (a == j) ? wslot.find({j, i}) : wslot.find({a, i});
+                if (ia == wslot.end()) continue;     // a is not in struct(i)
+                con.push_back(make_int2(ia->second, wslot[{j, i}]));
+            }
+            con_ptr.push_back((int)con.size());
+        }
+        for (int ei : contrib_of[j]) rc.push_back(make_int2(wslot[{j, enode[ei]}], ei));
+        rc_ptr.push_back((int)rc.size());
+    }
+    // tail
+    std::vector<int> rnode;
+    for (int v = 0; v < F; ++v) if (alive[v]) rnode.push_back(v);
+    std::vector<int2> blk, tcon, trc;
+    std::vector<int> tcon_ptr{0}, trc_ptr{0};
+    for (int ra = 0; ra < nR; ++ra) {
+        const int a = rnode[ra];
+        for (int rb = 0; rb <= ra; ++rb) {
+            const int b = rnode[rb];
+            blk.push_back(make_int2(ra, rb));
+            // contributors: i with a and b in struct(i) (both lists are in elimination order)
+            const auto &ca = contrib_of[a], &cb = contrib_of[b];
+            size_t x = 0, y = 0;
+            while (x < ca.size() && y < cb.size()) {
+                if (ca[x] < cb[y]) ++x;
+                else if (ca[x] > cb[y]) ++y;
+                else {
+                    const int i = enode[ca[x]];
+                    tcon.push_back(make_int2(wslot[{a, i}], wslot[{b, i}]));
+                    ++x; ++y;
+                }
+            }
+            tcon_ptr.push_back((int)tcon.size());
+        }
+        for (int ei : contrib_of[a]) trc.push_back(make_int2(wslot[{a, enode[ei]}], ei));
+        trc_ptr.push_back((int)trc.size());
+    }
+    bool ok = true;
+    ok = ok && sp_upload(p, &p->sp.enode, enode) && sp_upload(p, &p->sp.row_ptr, row_ptr) &&
+         sp_upload(p, &p->sp.row_node, row_node) && sp_upload(p, &p->sp.con_ptr, con_ptr) &&
+         sp_upload(p, &p->sp.con, con) && sp_upload(p, &p->sp.rc_ptr, rc_ptr) && sp_upload(p, &p->sp.rc, rc) &&
+         sp_upload(p, &p->spt.rnode, rnode) && sp_upload(p, &p->spt.blk, blk) &&
+         sp_upload(p, &p->spt.con_ptr, tcon_ptr) && sp_upload(p, &p->spt.con, tcon) &&
+         sp_upload(p, &p->spt.rc_ptr, trc_ptr) && sp_upload(p, &p->spt.rc, trc);
+    auto dalloc = [&](double** d, size_t n) {
+        if (cudaMalloc((void**)d, sizeof(double) * std::max<size_t>(n, 1)) != cudaSuccess) return false;
+        p->sp_allocs.push_back(*d);
+        return cudaMemset(*d, 0, sizeof(double) * std::max<size_t>(n, 1)) == cudaSuccess;
+    };
+    ok = ok && dalloc(&p->sp.W, (size_t)row_node.size() * 49) && dalloc(&p->sp.Ginv, (size_t)nE * 49) &&
+         dalloc(&p->sp.y, (size_t)nE * 7) && dalloc(&p->sp_Hr, (size_t)(npR + 1) * npR);
+    if (ok && npR > dimR) {   // identity on the padded diagonal, once: sp_tail_kernel never writes there
+        std::vector<double> ones(npR - dimR, 1.0);
+        ok = cudaMemcpy2D(p->sp_Hr + (size_t)dimR * npR + dimR, sizeof(double) * (npR + 1), ones.data(),
+                          sizeof(double), sizeof(double), npR - dimR, cudaMemcpyHostToDevice) == cudaSuccess;
+    }
+    if (!ok) { cudaGetLastError(); sp_free(p); return false; }
+    p->sp_nE = nE; p->sp_nR = nR; p->sp_dimR = dimR; p->sp_npR = npR;
+    p->sp_ntail_blocks = (int)blk.size();
+    p->sp_level_begin = level_begin;
+    p->sp_on = true;
     return true;
 }
 
@@ -3162,6 +3602,7 @@ M3S_API m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii, const int32_t* jj, in
     // assembly lists
     std::vector<BlockRef> blocks;
     std::vector<int> list_edge, list_sign;
+    std::vector<std::pair<int, int>> off_pairs;
     if (p->F > 0) {
         std::vector<std::vector<std::pair<int, int>>> diag(p->F);
         std::map<std::pair<int, int>, std::vector<int>> off;
@@ -3182,6 +3623,7 @@ M3S_API m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii, const int32_t* jj, in
             blocks.push_back(b);
         }
         for (auto& kv : off) {
+            off_pairs.push_back(kv.first);
             BlockRef b{kv.first.first, kv.first.second, (int)list_edge.size(), 0};
             for (int e : kv.second) { list_edge.push_back(e); list_sign.push_back(0); }
             b.end = (int)list_edge.size();
@@ -3244,6 +3686,7 @@ M3S_API m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii, const int32_t* jj, in
              cudaMemset(p->dx, 0, sizeof(double) * std::max(p->dim, 1)) == cudaSuccess &&
              cudaMemset(p->g, 0, sizeof(double) * std::max(p->dim, 1)) == cudaSuccess;
     }
+    if (ok && p->F > 0) ok = build_sparse_front(p, off_pairs);
     if (!ok) {
         cuda_fail(cudaGetLastError(), "gn_plan_create allocation");
         plan_free(p);
@@ -3568,6 +4011,24 @@ static int fused_grid_size(m3s_gn_plan* plan) {
 // Grid of the dataflow factorisation (chol_tiles_kernel): one CTA per diagonal tile + one per tile
 // (r, c) with r - c >= 2; every CTA must be co-resident (cooperative launch, 2 CTAs per SM).  0 = use
 // another path (M3S_GN_CHOL=steps|fused, no cooperative launch, or more tiles than resident CTAs).
+static int tiles_grid_for(m3s_gn_plan* plan, int np) {
+    int coop = 0, sms = 0, per_sm = 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, plan->device);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, plan->device);
+    if (!coop || sms <= 0 ||
+        cudaFuncSetAttribute(chol_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)sizeof(TilesSmem)) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chol_tiles_kernel, kTlThreads,
+                                                      sizeof(TilesSmem)) != cudaSuccess ||
+        per_sm < 1) {
+        cudaGetLastError();
+        return 0;
+    }
+    const int nt = (np + kTS - 1) / kTS;
+    const int grid = nt + nt * (nt - 1) / 2;
+    return grid > sms * per_sm ? 0 : grid;
+}
+
 static int tiles_grid_size(m3s_gn_plan* plan) {
     if (plan->tiles_grid >= 0) return plan->tiles_grid;
     plan->tiles_grid = 0;
@@ -3594,8 +4055,42 @@ static int tiles_grid_size(m3s_gn_plan* plan) {
 
 // assemble + blocked factorisation of the augmented matrix, enqueued on `st`: one cooperative launch
 // (chol_tiles_kernel, or chol_fused_kernel on request) or, as the fallback, one launch per block step
+// sparse front: levels, Schur complement on the tail, dataflow factorisation of the tail.  Returns 1 when the
+// tail's cooperative grid cannot be placed (the caller then factorises the whole system densely).
+static int enqueue_sparse_front(m3s_gn_plan* plan, cudaStream_t st, bool capturing) {
+    if (plan->sp_tiles_grid == 0) plan->sp_tiles_grid = tiles_grid_for(plan, plan->sp_npR);
+    if (plan->sp_tiles_grid == 0) { plan->sp_on = false; return 1; }
+    const int np = plan->np, npR = plan->sp_npR;
+    const int levels = (int)plan->sp_level_begin.size() - 1;
+    for (int l = 0; l < levels; ++l) {
+        const int b = plan->sp_level_begin[l], n = plan->sp_level_begin[l + 1] - b;
+        sp_level_kernel<<<n, kSpThreads, 0, st>>>(plan->status, plan->sp, b, plan->Hm, np);
+        if (int rc = launch_ok("sp_level_kernel")) return rc;
+    }
+    sp_tail_kernel<<<plan->sp_ntail_blocks, 64, 0, st>>>(plan->status, plan->sp, plan->spt, plan->Hm, np,
+                                                         plan->sp_Hr, npR);
+    if (int rc = launch_ok("sp_tail_kernel")) return rc;
+    const int nt = (npR + kTS - 1) / kTS, grid = plan->sp_tiles_grid;
+    M3S_CUDA(cudaMemsetAsync(plan->tctl, 0, sizeof(unsigned) * tl_ctl_words(nt), st));
+    int first_diag = std::max(0, std::min(sm_count_current(), grid) - nt);
+    void* args[] = {&plan->status, &plan->sp_Hr, &plan->Lm, &plan->Linv, const_cast<int*>(&npR),
+                    &plan->tctl, &first_diag, &plan->timeline};
+    const cudaError_t ce = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(chol_tiles_kernel), dim3(grid),
+                                                       dim3(kTlThreads), args, sizeof(TilesSmem), st);
+    if (ce == cudaSuccess) return launch_ok("chol_tiles_kernel");
+    cudaGetLastError();
+    if (capturing || (ce != cudaErrorCooperativeLaunchTooLarge && ce != cudaErrorLaunchOutOfResources))
+        return cuda_fail(ce, "cudaLaunchCooperativeKernel(chol_tiles_kernel, tail)");
+    plan->sp_on = false;   // the levels only wrote their own buffers: the dense paths start from Hm as assembled
+    return 1;
+}
+
 static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st, bool capturing = false) {
     if (int rc = m3s_gn_assemble(plan, reinterpret_cast<m3s_stream_t>(st))) return rc;
+    if (plan->sp_on) {
+        const int rc = enqueue_sparse_front(plan, st, capturing);
+        if (rc <= 0) return rc;
+    }
     const int np = plan->np;
     const int nblk = np / kNB;
     if (const int grid = tiles_grid_size(plan)) {
@@ -3670,7 +4165,7 @@ static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st, bool capt
 // written by the factorisation) it is done once here, on the caller's stream, outside the graph; on
 // the in-place paths it is forced into the graph.
 static void build_solve_graph(m3s_gn_plan* plan, cudaStream_t st) {
-    if (tiles_grid_size(plan) > 0) {
+    if (plan->sp_on || tiles_grid_size(plan) > 0) {   // neither path writes Hm
         if (!plan->hm_clean) {
             if (cudaMemsetAsync(plan->Hm, 0, sizeof(double) * (size_t)(plan->np + 1) * plan->np, st) != cudaSuccess) {
                 plan->graph_failed = true; cudaGetLastError(); return;
@@ -3698,8 +4193,22 @@ static void build_solve_graph(m3s_gn_plan* plan, cudaStream_t st) {
 
 M3S_API int m3s_gn_plan_factor_path(m3s_gn_plan* plan) {
     if (!plan || plan->F == 0) return 0;
+    if (plan->sp_on) {   // 3 = sparse front + dataflow factorisation of the tail (if its grid can be placed)
+        if (plan->sp_tiles_grid == 0) plan->sp_tiles_grid = tiles_grid_for(plan, plan->sp_npR);
+        if (plan->sp_tiles_grid > 0) return 3;
+        plan->sp_on = false;
+    }
     if (tiles_grid_size(plan) > 0) return 2;
     return fused_grid_size(plan) > 0 ? 1 : 0;
+}
+
+M3S_API int m3s_gn_plan_sparse_info(const m3s_gn_plan* plan, int32_t* out) {
+    M3S_REQUIRE(plan && out, "gn_plan_sparse_info: null pointer");
+    out[0] = plan->sp_on ? (int)plan->sp_level_begin.size() - 1 : 0;
+    out[1] = plan->sp_on ? plan->sp_nE : 0;
+    out[2] = plan->sp_on ? plan->sp_nR : plan->F;
+    out[3] = plan->sp_on ? plan->sp_npR : plan->np;
+    return M3S_OK;
 }
 
 M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_stream_t stream) {
@@ -3710,7 +4219,7 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
     // M3S_GN_GRAPH=0 launches directly (A/B, debugging)
     static const bool use_graph = [] { const char* e = getenv("M3S_GN_GRAPH"); return !(e && e[0] == '0'); }();
     if (use_graph && !plan->graph_exec && !plan->graph_failed &&
-        (tiles_grid_size(plan) > 0 || (np > 2 * kNB && fused_grid_size(plan) == 0)))
+        (plan->sp_on || tiles_grid_size(plan) > 0 || (np > 2 * kNB && fused_grid_size(plan) == 0)))
         build_solve_graph(plan, st);
     bool launched = false;
     if (plan->graph_exec) {
@@ -3729,6 +4238,24 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
     if (!launched) {
         if (int rc = enqueue_assemble_factor(plan, st)) return rc;
     }
+    const int metal = gp->semantics == M3S_SEM_METAL ? 1 : 0;
+    if (plan->sp_on) {
+        // dense back-substitution of the tail, then the levels in reverse, then the ||dx|| test + retraction
+        const int npR = plan->sp_npR, nblkR = npR / kNB;
+        gn_backsolve_group_kernel<<<(nblkR + kBackGroup - 1) / kBackGroup, kBackThreads, 0, st>>>(
+            plan->status, plan->Lm, plan->Linv, npR, plan->sp_dimR, plan->F, plan->free_kf, gp->delta_thresh,
+            plan->xsol, plan->flags, 1, plan->dx, plan->poses, plan->timeline, metal, 0);
+        if (int rc = launch_ok("gn_backsolve_group_kernel")) return rc;
+        sp_scatter_tail_kernel<<<(plan->sp_dimR + 255) / 256, 256, 0, st>>>(plan->status, plan->spt.rnode, plan->sp_nR,
+                                                                            plan->xsol, plan->dx);
+        for (int l = (int)plan->sp_level_begin.size() - 2; l >= 0; --l) {
+            const int b = plan->sp_level_begin[l], n = plan->sp_level_begin[l + 1] - b;
+            sp_back_kernel<<<n, 64, 0, st>>>(plan->status, plan->sp, b, plan->dx);
+        }
+        sp_finish_kernel<<<1, kBackThreads, 0, st>>>(plan->status, plan->dx, plan->dim, plan->F, plan->free_kf,
+                                                     gp->delta_thresh, plan->poses, metal);
+        return launch_ok("sp_finish_kernel");
+    }
     // M3S_GN_BACKSOLVE=block: one CTA per 32-column block (round 1); read per call (A/B, tests)
     const char* bse = getenv("M3S_GN_BACKSOLVE");
     const bool per_block = bse && strcmp(bse, "block") == 0;
@@ -3737,12 +4264,11 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
         gn_backsolve_update_kernel<<<nblk, kBackThreads, 0, st>>>(
             plan->status, plan->Lm, plan->Linv, np, plan->dim, plan->F, plan->free_kf, gp->delta_thresh,
             plan->xsol, plan->flags, 1, plan->dx, plan->poses, plan->timeline,
-            gp->semantics == M3S_SEM_METAL ? 1 : 0);
+            metal);
     else
         gn_backsolve_group_kernel<<<(nblk + kBackGroup - 1) / kBackGroup, kBackThreads, 0, st>>>(
             plan->status, plan->Lm, plan->Linv, np, plan->dim, plan->F, plan->free_kf, gp->delta_thresh,
-            plan->xsol, plan->flags, 1, plan->dx, plan->poses, plan->timeline,
-            gp->semantics == M3S_SEM_METAL ? 1 : 0);
+            plan->xsol, plan->flags, 1, plan->dx, plan->poses, plan->timeline, metal, 1);
     return launch_ok("gn_backsolve_update_kernel");
 }
 

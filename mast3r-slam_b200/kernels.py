@@ -441,9 +441,16 @@ class GNPlan:
 
     def factor_path(self) -> int:
         """0 = one launch per block step, 1 = persistent chain + workers, 2 = dataflow over
-        shared-memory-resident tiles (m3s_gn_plan_factor_path; decided at the first solve of the plan
-        from M3S_GN_CHOL and what is co-resident on the device)"""
+        shared-memory-resident tiles, 3 = sparse front + path 2 on the dense tail
+        (m3s_gn_plan_factor_path; decided from M3S_GN_CHOL / M3S_GN_SPARSE, the graph and what is
+        co-resident on the device)"""
         return int(_lib.load().m3s_gn_plan_factor_path(self.handle))
+
+    def sparse_info(self) -> dict:
+        """levels / eliminated keyframes / tail keyframes / padded tail dimension of the sparse front"""
+        out = (C.c_int32 * 4)()
+        _lib.check(_lib.load().m3s_gn_plan_sparse_info(self.handle, out))
+        return {"levels": int(out[0]), "eliminated": int(out[1]), "tail": int(out[2]), "tail_np": int(out[3])}
 
     def dx(self) -> torch.Tensor:
         return self._view(self._lib.m3s_gn_plan_dx(self.handle), self.dim)

@@ -350,7 +350,8 @@ def test_solve_paths_agree(K, synth, monkeypatch, num_kf, loops, precision):
     lib = _lib.load()
     p = lambda x: C.c_void_p(x.data_ptr())  # noqa: E731
     res = {}
-    for chol, back in (("steps", "block"), ("steps", "group"), ("fused", "group"), ("tiles", "group"), ("tiles", "block")):
+    for chol, back in (("steps", "block"), ("steps", "group"), ("fused", "group"), ("tiles", "group"), ("tiles", "block"),
+                       ("sparse", "group")):
         monkeypatch.setenv("M3S_GN_CHOL", chol)
         monkeypatch.setenv("M3S_GN_BACKSOLVE", back)
         plan = K.GNPlan(g["ii"], g["jj"], num_kf, 1024, 1, dev)
@@ -363,7 +364,7 @@ def test_solve_paths_agree(K, synth, monkeypatch, num_kf, loops, precision):
         assert st["applied"] == 1 and not st["failed"], (chol, back, st)
         res[(chol, back)] = (plan.factor_path(), plan.dx().cpu().numpy().copy(), plan.poses().cpu().numpy().copy())
         del plan
-    assert res[("steps", "block")][0] == 0 and res[("tiles", "group")][0] == 2
+    assert res[("steps", "block")][0] == 0 and res[("tiles", "group")][0] == 2 and res[("sparse", "group")][0] == 3
     ref_dx, ref_pose = res[("steps", "block")][1:]
     scale = np.abs(ref_dx).max()
     for key, (_, dx, pose) in res.items():
