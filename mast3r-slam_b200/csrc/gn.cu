@@ -3006,7 +3006,7 @@ gn_backsolve_group_kernel(Status* __restrict__ status, const double* __restrict_
 // rank.  H (Hm) is only read.
 // ------------------------------------------------------------------------------------------------
 constexpr int kSpMaxRows = 25;      // 1 + the largest struct a level keyframe may have
-constexpr int kSpThreads = 256;     // 4 groups of 64 (49 active) -- one 7x7 block per group at a time
+constexpr int kSpThreads = 1024;    // 16 groups of 64 (49 active) -- one 7x7 block per group at a time
 
 struct SpDev {
     const int* enode;      // [nE] free index of the eliminated keyframes, level-major
@@ -3020,6 +3020,35 @@ struct SpDev {
     double* Ginv;          // [nE][49]
     double* y;             // [nE][7]
 };
+
+// sum over a contributor list of the 7-term products  Wa[r, :] . Wb[c, :]  (rows of two 7x7 blocks), four list
+// entries per round so that their index and block loads are in flight together (the lists are short and every
+// load is an L2 round trip: taken one by one, a 25-entry list costs ~15k clk); fixed order, deterministic
+__device__ __forceinline__ double sp_dot7(const double* __restrict__ a, const double* __restrict__ b) {
+    double d = 0.0;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) d = fma(a[k], b[k], d);
+    return d;
+}
+__device__ __forceinline__ double sp_list_sum(const int2* __restrict__ lst, int q0, int q1,
+                                              const double* __restrict__ Wa, int ra, const double* __restrict__ Wb,
+                                              int rb, int sb) {
+    double acc = 0.0;
+    int q = q0;
+    for (; q + 4 <= q1; q += 4) {
+        const int2 w0 = lst[q], w1 = lst[q + 1], w2 = lst[q + 2], w3 = lst[q + 3];
+        const double d0 = sp_dot7(Wa + (size_t)w0.x * 49 + ra, Wb + (size_t)w0.y * sb + rb);
+        const double d1 = sp_dot7(Wa + (size_t)w1.x * 49 + ra, Wb + (size_t)w1.y * sb + rb);
+        const double d2 = sp_dot7(Wa + (size_t)w2.x * 49 + ra, Wb + (size_t)w2.y * sb + rb);
+        const double d3 = sp_dot7(Wa + (size_t)w3.x * 49 + ra, Wb + (size_t)w3.y * sb + rb);
+        acc += (d0 + d1) + (d2 + d3);
+    }
+    for (; q < q1; ++q) {
+        const int2 w = lst[q];
+        acc += sp_dot7(Wa + (size_t)w.x * 49 + ra, Wb + (size_t)w.y * sb + rb);
+    }
+    return acc;
+}
 
 __global__ void __launch_bounds__(kSpThreads)
 sp_level_kernel(Status* __restrict__ status, SpDev sp, int e_begin, const double* __restrict__ Hm, int np) {
@@ -3035,62 +3064,59 @@ sp_level_kernel(Status* __restrict__ status, SpDev sp, int e_begin, const double
     for (int s = grp; s < nrows; s += kSpThreads / 64) {
         if (t < 49) {
             const int a = sp.row_node[r0 + s];
-            double acc = Hm[(size_t)(7 * a + r) * np + 7 * j + c];
-            for (int q = sp.con_ptr[r0 + s]; q < sp.con_ptr[r0 + s + 1]; ++q) {
-                const int2 w = sp.con[q];
-                const double* wa = sp.W + (size_t)w.x * 49 + r * 7;
-                const double* wj = sp.W + (size_t)w.y * 49 + c * 7;
-                double d = 0.0;
-#pragma unroll
-                for (int k = 0; k < 7; ++k) d = fma(wa[k], wj[k], d);
-                acc -= d;
-            }
-            At[s][t] = acc;
+            // (the W slots read here were written by earlier launches, never by this one)
+            At[s][t] = Hm[(size_t)(7 * a + r) * np + 7 * j + c] -
+                       sp_list_sum(sp.con, sp.con_ptr[r0 + s], sp.con_ptr[r0 + s + 1], sp.W, r * 7, sp.W, c * 7, 49);
         } else if (s == 0 && t < 56) {
             const int rr = t - 49;
-            double acc = Hm[(size_t)np * np + 7 * j + rr];
-            for (int q = sp.rc_ptr[e]; q < sp.rc_ptr[e + 1]; ++q) {
-                const int2 w = sp.rc[q];
-                const double* wj = sp.W + (size_t)w.x * 49 + rr * 7;
-                const double* yi = sp.y + (size_t)w.y * 7;
-                double d = 0.0;
-#pragma unroll
-                for (int k = 0; k < 7; ++k) d = fma(wj[k], yi[k], d);
-                acc -= d;
-            }
-            bt[rr] = acc;
+            bt[rr] = Hm[(size_t)np * np + 7 * j + rr] -
+                     sp_list_sum(sp.rc, sp.rc_ptr[e], sp.rc_ptr[e + 1], sp.W, rr * 7, sp.y, 0, 7);
         }
     }
     __syncthreads();
-    if (tid < 7) {   // column tid of G^-1 after thread 0's Cholesky: 7x7, latency only
-        if (tid == 0) {
-            bool bad = false;
-            for (int k = 0; k < 7; ++k) {
-                double d = At[0][k * 7 + k];
-                for (int m = 0; m < k; ++m) d -= At[0][k * 7 + m] * At[0][k * 7 + m];
-                if (!(d > 0.0)) { bad = true; d = 1.0; }
-                const double g = sqrt(d), gi = 1.0 / g;
-                At[0][k * 7 + k] = g;
-                for (int i = k + 1; i < 7; ++i) {
-                    double v = At[0][i * 7 + k];
-                    for (int m = 0; m < k; ++m) v -= At[0][i * 7 + m] * At[0][k * 7 + m];
-                    At[0][i * 7 + k] = v * gi;
-                }
+    if (tid == 0) {
+        // 7x7 Cholesky and G^-1 by one thread, everything in registers (fully unrolled): the block is on the
+        // critical path of the level, and 28 + 28 values through shared memory with IEEE sqrt / division took
+        // longer than the rest of the kernel
+        double g[7][7], gi[7], v[7][7];
+        bool bad = false;
+#pragma unroll
+        for (int i = 0; i < 7; ++i)
+#pragma unroll
+            for (int k = 0; k <= i; ++k) g[i][k] = At[0][i * 7 + k];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            double d = g[k][k];
+#pragma unroll
+            for (int m = 0; m < k; ++m) d = fma(-g[k][m], g[k][m], d);
+            if (!(d > 0.0) || !(d <= 1.7e308)) { bad = true; d = 1.0; }
+            gi[k] = rsqrt_fast(d);
+            g[k][k] = d * gi[k];
+#pragma unroll
+            for (int i = k + 1; i < 7; ++i) {
+                double x = g[i][k];
+#pragma unroll
+                for (int m = 0; m < k; ++m) x = fma(-g[i][m], g[k][m], x);
+                g[i][k] = x * gi[k];
             }
-            if (bad) status->chol_fail = 1;
         }
-        __syncwarp(0x7fu);
-        double x[7];
+        // V = G^-1 (lower): V_ii = 1 / G_ii, V_ij = -V_ii sum_{k = j .. i-1} G_ik V_kj
 #pragma unroll
-        for (int i = 0; i < 7; ++i) {   // G x = e_tid
-            double v = (i == tid) ? 1.0 : 0.0;
+        for (int j = 0; j < 7; ++j) {
+            v[j][j] = gi[j];
 #pragma unroll
-            for (int m = 0; m < 7; ++m)
-                if (m < i) v -= At[0][i * 7 + m] * x[m];
-            x[i] = v / At[0][i * 7 + i];
+            for (int i = j + 1; i < 7; ++i) {
+                double x = 0.0;
+#pragma unroll
+                for (int k = j; k < i; ++k) x = fma(g[i][k], v[k][j], x);
+                v[i][j] = -x * gi[i];
+            }
         }
 #pragma unroll
-        for (int i = 0; i < 7; ++i) Gi[i * 7 + tid] = x[i];
+        for (int i = 0; i < 7; ++i)
+#pragma unroll
+            for (int j = 0; j < 7; ++j) Gi[i * 7 + j] = (j <= i) ? v[i][j] : 0.0;
+        if (bad) status->chol_fail = 1;
     }
     __syncthreads();
     for (int s = 1 + grp; s < nrows; s += kSpThreads / 64) {
@@ -3131,91 +3157,74 @@ sp_tail_kernel(const Status* __restrict__ status, SpDev sp, SpTailDev tl, const 
     const int t = threadIdx.x;
     if (t < 49) {
         const int r = t / 7, c = t % 7;
-        double acc = Hm[(size_t)(7 * a + r) * np + 7 * b + c];
-        for (int q = tl.con_ptr[blockIdx.x]; q < tl.con_ptr[blockIdx.x + 1]; ++q) {
-            const int2 w = tl.con[q];
-            const double* wa = sp.W + (size_t)w.x * 49 + r * 7;
-            const double* wb = sp.W + (size_t)w.y * 49 + c * 7;
-            double d = 0.0;
-#pragma unroll
-            for (int k = 0; k < 7; ++k) d = fma(wa[k], wb[k], d);
-            acc -= d;
-        }
+        const double acc = Hm[(size_t)(7 * a + r) * np + 7 * b + c] -
+                           sp_list_sum(tl.con, tl.con_ptr[blockIdx.x], tl.con_ptr[blockIdx.x + 1], sp.W, r * 7, sp.W, c * 7, 49);
         Hr[(size_t)(7 * rb.x + r) * npR + 7 * rb.y + c] = acc;
         if (rb.x != rb.y) Hr[(size_t)(7 * rb.y + c) * npR + 7 * rb.x + r] = acc;
     } else if (rb.x == rb.y && t < 56) {
         const int rr = t - 49;
-        double acc = Hm[(size_t)np * np + 7 * a + rr];
-        for (int q = tl.rc_ptr[rb.x]; q < tl.rc_ptr[rb.x + 1]; ++q) {
-            const int2 w = tl.rc[q];
-            const double* wa = sp.W + (size_t)w.x * 49 + rr * 7;
-            const double* yi = sp.y + (size_t)w.y * 7;
-            double d = 0.0;
-#pragma unroll
-            for (int k = 0; k < 7; ++k) d = fma(wa[k], yi[k], d);
-            acc -= d;
-        }
-        Hr[(size_t)npR * npR + 7 * rb.x + rr] = acc;
+        Hr[(size_t)npR * npR + 7 * rb.x + rr] =
+            Hm[(size_t)np * np + 7 * a + rr] -
+            sp_list_sum(tl.rc, tl.rc_ptr[rb.x], tl.rc_ptr[rb.x + 1], sp.W, rr * 7, sp.y, 0, 7);
     }
 }
 
-// x of the tail (dense back-substitution result, tail order) into the natural-order step vector
-__global__ void sp_scatter_tail_kernel(const Status* __restrict__ status, const int* __restrict__ rnode, int nR,
-                                       const double* __restrict__ xsol, double* __restrict__ dx) {
+// The whole back end of the sparse-front solve in ONE CTA: tail x into natural order, the levels in reverse
+// (x_j = G^-T (y_j - sum_a W_aj^T x_a); 16 keyframes at a time, 56 threads each), the ||dx|| test before applying
+// (gauss_newton.py:263-265) and the Sim3 retraction.  (As one launch per level + scatter + finish this was seven
+// launches of 3-10 us each for ~50k FMAs of work.)
+__global__ void __launch_bounds__(1024)
+sp_back_finish_kernel(Status* __restrict__ status, SpDev sp, const int* __restrict__ level_begin, int levels,
+                      const int* __restrict__ rnode, int nR, const double* __restrict__ xsol,
+                      double* __restrict__ dx, int dim, int num_free, const int* __restrict__ free_kf,
+                      double delta_thresh, double* __restrict__ poses, int metal) {
     if (status->stopped | status->failed) return;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < 7 * nR) dx[7 * rnode[i / 7] + i % 7] = xsol[i];
-}
-
-// one level of the back-substitution: x_j = G^-T (y_j - sum_a W_aj^T x_a), one 64-thread CTA per keyframe
-__global__ void __launch_bounds__(64)
-sp_back_kernel(const Status* __restrict__ status, SpDev sp, int e_begin, double* __restrict__ dx) {
-    if (status->stopped | status->failed) return;
-    __shared__ double part[8][7];
-    __shared__ double tv[7];
-    const int e = e_begin + blockIdx.x;
-    const int r0 = sp.row_ptr[e], nrows = sp.row_ptr[e + 1] - r0;
-    const int t = threadIdx.x;
-    if (t < 56) {
-        const int k = t % 7, p = t / 7;   // partial p of component k: rows s = 1 + p, 9 + p, ...
-        double acc = 0.0;
-        for (int s = 1 + p; s < nrows; s += 8) {
-            const double* w = sp.W + (size_t)(r0 + s) * 49 + k;
-            const double* xa = dx + 7 * sp.row_node[r0 + s];
-#pragma unroll
-            for (int r = 0; r < 7; ++r) acc = fma(w[r * 7], xa[r], acc);
-        }
-        part[p][k] = acc;
-    }
-    __syncthreads();
-    if (t < 7) {
-        double v = sp.y[(size_t)e * 7 + t];
-#pragma unroll
-        for (int p = 0; p < 8; ++p) v -= part[p][t];
-        tv[t] = v;
-    }
-    __syncthreads();
-    if (t < 7) {
-        const double* gi = sp.Ginv + (size_t)e * 49;
-        double d = 0.0;
-#pragma unroll
-        for (int k = 0; k < 7; ++k) d = fma(gi[k * 7 + t], tv[k], d);
-        dx[7 * sp.enode[e] + t] = d;
-    }
-}
-
-// ||dx|| test before applying (gauss_newton.py:263-265) and the Sim3 retraction, as the tail of the dense
-// back-substitution kernels, for the sparse-front path (dx is complete in natural order)
-__global__ void __launch_bounds__(kBackThreads)
-sp_finish_kernel(Status* __restrict__ status, const double* __restrict__ dx, int dim, int num_free,
-                 const int* __restrict__ free_kf, double delta_thresh, double* __restrict__ poses, int metal) {
-    if (status->stopped | status->failed) return;
-    const int tid = threadIdx.x;
-    __shared__ double red[kBackThreads / 32];
+    __shared__ double part[16][8][7];
+    __shared__ double tv[16][7];
+    __shared__ double red[32];
     __shared__ int decision;  // 0 apply, 1 stop, 2 fail
+    const int tid = threadIdx.x, grp = tid >> 6, t = tid & 63;
+    for (int i = tid; i < 7 * nR; i += 1024) dx[7 * rnode[i / 7] + i % 7] = __ldcg(xsol + i);
+    __syncthreads();
+    for (int l = levels - 1; l >= 0; --l) {
+        const int b = level_begin[l], n = level_begin[l + 1] - b;
+        for (int it = 0; it < n; it += 16) {
+            const int e = b + it + grp;
+            const bool on = it + grp < n;
+            int r0 = 0, nrows = 0;
+            if (on) { r0 = sp.row_ptr[e]; nrows = sp.row_ptr[e + 1] - r0; }
+            if (on && t < 56) {
+                const int k = t % 7, p = t / 7;   // partial p of component k: rows s = 1 + p, 9 + p, ...
+                double acc = 0.0;
+                for (int s = 1 + p; s < nrows; s += 8) {
+                    const double* w = sp.W + (size_t)(r0 + s) * 49 + k;
+                    const double* xa = dx + 7 * sp.row_node[r0 + s];
+#pragma unroll
+                    for (int r = 0; r < 7; ++r) acc = fma(w[r * 7], xa[r], acc);
+                }
+                part[grp][p][k] = acc;
+            }
+            __syncthreads();
+            if (on && t < 7) {
+                double v = sp.y[(size_t)e * 7 + t];
+#pragma unroll
+                for (int p = 0; p < 8; ++p) v -= part[grp][p][t];
+                tv[grp][t] = v;
+            }
+            __syncthreads();
+            if (on && t < 7) {
+                const double* gi = sp.Ginv + (size_t)e * 49;
+                double d = 0.0;
+#pragma unroll
+                for (int k = 0; k < 7; ++k) d = fma(gi[k * 7 + t], tv[grp][k], d);
+                dx[7 * sp.enode[e] + t] = d;
+            }
+        }
+        __syncthreads();   // the level's x is visible to the whole CTA before the next level reads it
+    }
     double psum = 0.0;
     int nonfinite = 0;
-    for (int i = tid; i < dim; i += kBackThreads) {
+    for (int i = tid; i < dim; i += 1024) {
         const double v = dx[i];
         psum += v * v;
         if (!(fabs(v) <= 1.7e308)) nonfinite = 1;
@@ -3226,7 +3235,7 @@ sp_finish_kernel(Status* __restrict__ status, const double* __restrict__ dx, int
     __syncthreads();
     if (tid == 0) {
         double s = 0.0;
-        for (int w = 0; w < kBackThreads / 32; ++w) s += red[w];
+        for (int w = 0; w < 32; ++w) s += red[w];
         const double nrm = sqrt(s);
         status->last_norm = nrm;
         status->attempted += 1;
@@ -3241,7 +3250,7 @@ sp_finish_kernel(Status* __restrict__ status, const double* __restrict__ dx, int
     }
     __syncthreads();
     if (decision != 0) return;
-    for (int f = tid; f < num_free; f += kBackThreads) {
+    for (int f = tid; f < num_free; f += 1024) {
         double xi[7];
 #pragma unroll
         for (int k = 0; k < 7; ++k) xi[k] = dx[7 * f + k];
@@ -3306,6 +3315,7 @@ struct m3s_gn_plan {
     bool sp_on = false;
     int sp_nE = 0, sp_nR = 0, sp_dimR = 0, sp_npR = 0, sp_ntail_blocks = 0;
     std::vector<int> sp_level_begin;   // [levels + 1] into the level-major list of eliminated keyframes
+    const int* sp_level_begin_d = nullptr;
     SpDev sp{};
     SpTailDev spt{};
     double* sp_Hr = nullptr;           // [npR + 1, npR] Schur complement on the tail (+ rhs row)
@@ -3429,7 +3439,10 @@ static bool build_sparse_front(m3s_gn_plan* p, const std::vector<std::pair<int, 
     std::vector<int> elim_pos(F, -1);        // e index (level-major) of an eliminated keyframe
     std::vector<int> enode, level_begin{0};
     int n_alive = F;
-    for (int l = 0; l < kSpMaxLevels; ++l) {
+    int min_level = kSpMinLevel, max_levels = kSpMaxLevels;   // M3S_GN_SP_MINLEVEL / _MAXLEVELS: A/B knobs
+    if (const char* e = getenv("M3S_GN_SP_MINLEVEL")) min_level = std::max(1, atoi(e));
+    if (const char* e = getenv("M3S_GN_SP_MAXLEVELS")) max_levels = std::max(1, atoi(e));
+    for (int l = 0; l < max_levels; ++l) {
         std::vector<std::pair<int, int>> cand;
         for (int v = 0; v < F; ++v)
             if (alive[v] && (int)adj[v].size() <= kSpMaxRows - 1) cand.push_back({(int)adj[v].size(), v});
@@ -3443,7 +3456,7 @@ static bool build_sparse_front(m3s_gn_plan* p, const std::vector<std::pair<int, 
             blocked[v] = 1;
             for (int n : adj[v]) blocked[n] = 1;
         }
-        if ((int)sel.size() < (forced ? 1 : kSpMinLevel)) break;
+        if ((int)sel.size() < (forced ? 1 : min_level)) break;
         std::sort(sel.begin(), sel.end());
         for (int v : sel) {
             strct[v].assign(adj[v].begin(), adj[v].end());
@@ -3526,7 +3539,8 @@ static bool build_sparse_front(m3s_gn_plan* p, const std::vector<std::pair<int, 
          sp_upload(p, &p->sp.con, con) && sp_upload(p, &p->sp.rc_ptr, rc_ptr) && sp_upload(p, &p->sp.rc, rc) &&
          sp_upload(p, &p->spt.rnode, rnode) && sp_upload(p, &p->spt.blk, blk) &&
          sp_upload(p, &p->spt.con_ptr, tcon_ptr) && sp_upload(p, &p->spt.con, tcon) &&
-         sp_upload(p, &p->spt.rc_ptr, trc_ptr) && sp_upload(p, &p->spt.rc, trc);
+         sp_upload(p, &p->spt.rc_ptr, trc_ptr) && sp_upload(p, &p->spt.rc, trc) &&
+         sp_upload(p, &p->sp_level_begin_d, level_begin);
     auto dalloc = [&](double** d, size_t n) {
         if (cudaMalloc((void**)d, sizeof(double) * std::max<size_t>(n, 1)) != cudaSuccess) return false;
         p->sp_allocs.push_back(*d);
@@ -3954,7 +3968,7 @@ M3S_API int m3s_gn_assemble(m3s_gn_plan* plan, m3s_stream_t stream) {
                                                        plan->list_sign, plan->edge_blocks, plan->Hm,
                                                        plan->np, plan->dim, plan->g);
     if (int rc = launch_ok("gn_assemble_kernel")) return rc;
-    if (plan->np > plan->dim) {
+    if (plan->np > plan->dim && !plan->sp_on) {   // (the sparse front reads keyframe blocks only)
         gn_pad_diag_kernel<<<1, 32, 0, st>>>(plan->status, plan->Hm, plan->np, plan->dim);
         if (int rc = launch_ok("gn_pad_diag_kernel")) return rc;
     }
@@ -4090,6 +4104,10 @@ static int enqueue_assemble_factor(m3s_gn_plan* plan, cudaStream_t st, bool capt
     if (plan->sp_on) {
         const int rc = enqueue_sparse_front(plan, st, capturing);
         if (rc <= 0) return rc;
+        if (plan->np > plan->dim) {   // dense fallback: m3s_gn_assemble skipped the padding for the sparse front
+            gn_pad_diag_kernel<<<1, 32, 0, st>>>(plan->status, plan->Hm, plan->np, plan->dim);
+            if (int rc2 = launch_ok("gn_pad_diag_kernel")) return rc2;
+        }
     }
     const int np = plan->np;
     const int nblk = np / kNB;
@@ -4246,15 +4264,11 @@ M3S_API int m3s_gn_solve_update(m3s_gn_plan* plan, const m3s_gn_params* gp, m3s_
             plan->status, plan->Lm, plan->Linv, npR, plan->sp_dimR, plan->F, plan->free_kf, gp->delta_thresh,
             plan->xsol, plan->flags, 1, plan->dx, plan->poses, plan->timeline, metal, 0);
         if (int rc = launch_ok("gn_backsolve_group_kernel")) return rc;
-        sp_scatter_tail_kernel<<<(plan->sp_dimR + 255) / 256, 256, 0, st>>>(plan->status, plan->spt.rnode, plan->sp_nR,
-                                                                            plan->xsol, plan->dx);
-        for (int l = (int)plan->sp_level_begin.size() - 2; l >= 0; --l) {
-            const int b = plan->sp_level_begin[l], n = plan->sp_level_begin[l + 1] - b;
-            sp_back_kernel<<<n, 64, 0, st>>>(plan->status, plan->sp, b, plan->dx);
-        }
-        sp_finish_kernel<<<1, kBackThreads, 0, st>>>(plan->status, plan->dx, plan->dim, plan->F, plan->free_kf,
-                                                     gp->delta_thresh, plan->poses, metal);
-        return launch_ok("sp_finish_kernel");
+        sp_back_finish_kernel<<<1, 1024, 0, st>>>(plan->status, plan->sp, plan->sp_level_begin_d,
+                                                  (int)plan->sp_level_begin.size() - 1, plan->spt.rnode, plan->sp_nR,
+                                                  plan->xsol, plan->dx, plan->dim, plan->F, plan->free_kf,
+                                                  gp->delta_thresh, plan->poses, metal);
+        return launch_ok("sp_back_finish_kernel");
     }
     // M3S_GN_BACKSOLVE=block: one CTA per 32-column block (round 1); read per call (A/B, tests)
     const char* bse = getenv("M3S_GN_BACKSOLVE");
