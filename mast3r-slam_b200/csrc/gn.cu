@@ -3006,7 +3006,7 @@ gn_backsolve_group_kernel(Status* __restrict__ status, const double* __restrict_
 // rank.  H (Hm) is only read.
 // ------------------------------------------------------------------------------------------------
 constexpr int kSpMaxRows = 25;      // 1 + the largest struct a level keyframe may have
-constexpr int kSpThreads = 1024;    // 16 groups of 64 (49 active) -- one 7x7 block per group at a time
+constexpr int kSpThreads = 32 * (kSpMaxRows + 1);   // one warp per row block + one for the right-hand side
 
 struct SpDev {
     const int* enode;      // [nE] free index of the eliminated keyframes, level-major
@@ -3050,28 +3050,72 @@ __device__ __forceinline__ double sp_list_sum(const int2* __restrict__ lst, int 
     return acc;
 }
 
+// One CTA per keyframe of the level, ONE WARP PER ROW BLOCK (rows <= 25) + one warp for the right-hand side.
+// A row's contributor list is walked four entries at a time: the warp loads the 4 x (W_ai, W_ji) blocks -- 392
+// doubles, 12-13 independent coalesced loads per lane, all in flight together -- into its slice of shared memory
+// and every lane then forms its two entries of the 7x7 block from there.  (One thread per entry loading its own
+// 14 doubles per contributor kept too few loads in flight: 10-18 us per level for a few MFLOP.)
+constexpr int kSpBatch = 4;
+constexpr int kSpStage = kSpBatch * 98;                       // doubles per warp
+constexpr size_t kSpLevelSmem = sizeof(double) * kSpStage * kSpMaxRows;
+
 __global__ void __launch_bounds__(kSpThreads)
 sp_level_kernel(Status* __restrict__ status, SpDev sp, int e_begin, const double* __restrict__ Hm, int np) {
     if (status->stopped | status->failed) return;
+    extern __shared__ __align__(16) double sp_stage[];
     __shared__ double At[kSpMaxRows][49];
     __shared__ double Gi[49];
     __shared__ double bt[7];
     const int e = e_begin + blockIdx.x;
     const int j = sp.enode[e];
     const int r0 = sp.row_ptr[e], nrows = sp.row_ptr[e + 1] - r0;
-    const int tid = threadIdx.x, grp = tid >> 6, t = tid & 63;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int grp = tid >> 6, t = tid & 63;
     const int r = t / 7, c = t % 7;
-    for (int s = grp; s < nrows; s += kSpThreads / 64) {
-        if (t < 49) {
-            const int a = sp.row_node[r0 + s];
-            // (the W slots read here were written by earlier launches, never by this one)
-            At[s][t] = Hm[(size_t)(7 * a + r) * np + 7 * j + c] -
-                       sp_list_sum(sp.con, sp.con_ptr[r0 + s], sp.con_ptr[r0 + s + 1], sp.W, r * 7, sp.W, c * 7, 49);
-        } else if (s == 0 && t < 56) {
-            const int rr = t - 49;
-            bt[rr] = Hm[(size_t)np * np + 7 * j + rr] -
-                     sp_list_sum(sp.rc, sp.rc_ptr[e], sp.rc_ptr[e + 1], sp.W, rr * 7, sp.y, 0, 7);
+    const double* __restrict__ Wr = sp.W;   // (the slots read here were written by earlier launches, never by this one)
+    if (warp < nrows) {
+        const int s = warp;
+        const int a = sp.row_node[r0 + s];
+        double* st = sp_stage + (size_t)warp * kSpStage;
+        const int t0 = lane, t1 = lane + 32;                  // this lane's entries of the block (t1 < 49: lanes 0 .. 16)
+        const int ra0 = (t0 / 7) * 7, cb0 = 49 + (t0 % 7) * 7;
+        const int ra1 = (t1 < 49 ? t1 / 7 : 0) * 7, cb1 = 49 + (t1 < 49 ? t1 % 7 : 0) * 7;
+        double acc0 = 0.0, acc1 = 0.0;
+        const int q0 = sp.con_ptr[r0 + s], q1 = sp.con_ptr[r0 + s + 1];
+        for (int q = q0; q < q1; q += kSpBatch) {
+            const int nb = min(kSpBatch, q1 - q);
+            int2 w = make_int2(0, 0);
+            if (lane < nb) w = sp.con[q + lane];
+            double v[(kSpStage + 31) / 32];
+#pragma unroll
+            for (int k = 0; k < (kSpStage + 31) / 32; ++k) {
+                const int idx = lane + 32 * k;
+                const int cc = idx / 98, off = idx % 98;
+                const int wx = __shfl_sync(0xffffffffu, w.x, cc & (kSpBatch - 1));
+                const int wy = __shfl_sync(0xffffffffu, w.y, cc & (kSpBatch - 1));
+                v[k] = 0.0;
+                if (idx < kSpStage && cc < nb)
+                    v[k] = (off < 49) ? Wr[(size_t)wx * 49 + off] : Wr[(size_t)wy * 49 + off - 49];
+            }
+            __syncwarp();                                     // the previous round's reads of the slice are done
+#pragma unroll
+            for (int k = 0; k < (kSpStage + 31) / 32; ++k)
+                if (lane + 32 * k < kSpStage) st[lane + 32 * k] = v[k];
+            __syncwarp();
+            double d0[kSpBatch], d1[kSpBatch];
+#pragma unroll
+            for (int cc = 0; cc < kSpBatch; ++cc) {          // entries past the end of the list were staged as zeros
+                d0[cc] = sp_dot7(st + cc * 98 + ra0, st + cc * 98 + cb0);
+                d1[cc] = sp_dot7(st + cc * 98 + ra1, st + cc * 98 + cb1);
+            }
+            acc0 += (d0[0] + d0[1]) + (d0[2] + d0[3]);
+            acc1 += (d1[0] + d1[1]) + (d1[2] + d1[3]);
         }
+        At[s][t0] = Hm[(size_t)(7 * a + t0 / 7) * np + 7 * j + t0 % 7] - acc0;
+        if (t1 < 49) At[s][t1] = Hm[(size_t)(7 * a + t1 / 7) * np + 7 * j + t1 % 7] - acc1;
+    } else if (warp == kSpMaxRows && lane < 7) {
+        bt[lane] = Hm[(size_t)np * np + 7 * j + lane] -
+                   sp_list_sum(sp.rc, sp.rc_ptr[e], sp.rc_ptr[e + 1], sp.W, lane * 7, sp.y, 0, 7);
     }
     __syncthreads();
     if (tid == 0) {
@@ -4073,12 +4117,17 @@ static int tiles_grid_size(m3s_gn_plan* plan) {
 // tail's cooperative grid cannot be placed (the caller then factorises the whole system densely).
 static int enqueue_sparse_front(m3s_gn_plan* plan, cudaStream_t st, bool capturing) {
     if (plan->sp_tiles_grid == 0) plan->sp_tiles_grid = tiles_grid_for(plan, plan->sp_npR);
-    if (plan->sp_tiles_grid == 0) { plan->sp_on = false; return 1; }
+    if (plan->sp_tiles_grid == 0 ||
+        cudaFuncSetAttribute(sp_level_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSpLevelSmem) != cudaSuccess) {
+        cudaGetLastError();
+        plan->sp_on = false;
+        return 1;
+    }
     const int np = plan->np, npR = plan->sp_npR;
     const int levels = (int)plan->sp_level_begin.size() - 1;
     for (int l = 0; l < levels; ++l) {
         const int b = plan->sp_level_begin[l], n = plan->sp_level_begin[l + 1] - b;
-        sp_level_kernel<<<n, kSpThreads, 0, st>>>(plan->status, plan->sp, b, plan->Hm, np);
+        sp_level_kernel<<<n, kSpThreads, kSpLevelSmem, st>>>(plan->status, plan->sp, b, plan->Hm, np);
         if (int rc = launch_ok("sp_level_kernel")) return rc;
     }
     sp_tail_kernel<<<plan->sp_ntail_blocks, 64, 0, st>>>(plan->status, plan->sp, plan->spt, plan->Hm, np,

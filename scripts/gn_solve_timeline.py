@@ -18,6 +18,8 @@ from mast3r_slam_b200 import _lib, kernels as K, synth  # noqa: E402
 
 
 def main():
+    # the stamps describe the dense chain over the whole system: keep the sparse front out unless asked for
+    os.environ.setdefault("M3S_GN_SPARSE", "0")
     dev = torch.device("cuda", 0)
     g = synth.make_graph(7, 200, 103, 48, 64, num_pts=512)
     plan = K.GNPlan(g["ii"], g["jj"], 200, 512, 1, dev)

@@ -373,3 +373,62 @@ def test_solve_paths_agree(K, synth, monkeypatch, num_kf, loops, precision):
     # the grouped back-substitution reads the same factor: bitwise equal to the per-block one
     assert np.array_equal(res[("tiles", "group")][1], res[("tiles", "block")][1]) or \
         np.abs(res[("tiles", "group")][1] - res[("tiles", "block")][1]).max() <= 1e-12 * scale
+
+
+def test_sparse_front_selection(K, synth, monkeypatch, precision):
+    """The sparse front (levels of exactly eliminated keyframes + dense tail) is chosen from the graph alone:
+    taken for the window-2 chain + loop closures of config 5, not for a complete graph (nothing to eliminate
+    cheaply) nor for systems of one tile; M3S_GN_SPARSE=0 keeps everything dense."""
+    import torch
+    if precision != "f64":
+        pytest.skip("plan-level property")
+    dev = torch.device("cuda", 0)
+    monkeypatch.delenv("M3S_GN_CHOL", raising=False)
+    monkeypatch.delenv("M3S_GN_SPARSE", raising=False)
+    rng = np.random.default_rng(5)
+    ii, jj = synth.graph_edges(200, 103, rng)
+    plan = K.GNPlan(ii, jj, 200, 1024, 1, dev)
+    info = plan.sparse_info()
+    assert info["levels"] >= 3 and info["eliminated"] + info["tail"] == plan.dim // 7
+    assert info["tail_np"] <= plan.ld // 2 and plan.factor_path() == 3
+    del plan
+    n = 30
+    a, b = np.triu_indices(n, 1)
+    ci, cj = np.concatenate([a, b]).astype(np.int32), np.concatenate([b, a]).astype(np.int32)
+    plan = K.GNPlan(ci, cj, n, 1024, 1, dev)
+    assert plan.sparse_info()["levels"] == 0 and plan.factor_path() == 2
+    del plan
+    ii, jj = synth.graph_edges(8, 1, rng)
+    plan = K.GNPlan(ii, jj, 8, 1024, 1, dev)
+    assert plan.sparse_info()["levels"] == 0
+    del plan
+    monkeypatch.setenv("M3S_GN_SPARSE", "0")
+    ii, jj = synth.graph_edges(200, 103, rng)
+    plan = K.GNPlan(ii, jj, 200, 1024, 1, dev)
+    assert plan.sparse_info()["levels"] == 0 and plan.factor_path() == 2
+
+
+@pytest.mark.parametrize("num_kf,loops", [(40, 10), (120, 40)])
+def test_sparse_front_iterations_and_stop(K, synth, monkeypatch, num_kf, loops):
+    """Whole solves through the sparse front against the dense dataflow path: several iterations (poses to
+    1e-9 of the pose scale), the same iteration count when the ||dx|| test stops the loop, and an untouched
+    pose array when the first step is already below the threshold (stop BEFORE applying, gauss_newton.py:263)."""
+    g = synth.make_graph(21, num_kf, loops, 48, 64, num_pts=2048)
+    a = gargs(g)
+    out = {}
+    for chol in ("tiles", "sparse"):
+        monkeypatch.setenv("M3S_GN_CHOL", chol)
+        K._plan_cache.clear()
+        out[chol] = (K.gauss_newton_points(*a, max_iter=6, delta_thresh=0.0),
+                     K.gauss_newton_points(*a, max_iter=10, delta_thresh=1e-4),
+                     K.gauss_newton_points(*a, max_iter=10, delta_thresh=1e9))
+        plan = K.get_plan(g["ii"], g["jj"], num_kf, 2048, 1, __import__("torch").device("cuda", 0))
+        assert plan.factor_path() == (3 if chol == "sparse" else 2)
+        out[chol] += (plan.status()["attempted"],)
+    K._plan_cache.clear()
+    scale = np.abs(g["Twc"]).max()
+    for k in range(2):
+        assert np.abs(out["sparse"][k].astype(np.float64) - out["tiles"][k]).max() <= 1e-6 * scale
+        assert upd_err(out["sparse"][k], out["tiles"][k], g["Twc"]) <= 1e-6
+    assert np.array_equal(out["sparse"][2], g["Twc"].astype(np.float32)) and np.array_equal(out["tiles"][2], out["sparse"][2])
+    assert out["sparse"][3] == out["tiles"][3]
