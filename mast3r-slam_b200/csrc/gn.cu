@@ -3448,7 +3448,7 @@ static bool dev_alloc_copy(T** dst, const std::vector<T>& src) {
 // explicit M3S_GN_CHOL=steps|fused|tiles keeps the whole system dense, M3S_GN_CHOL=sparse forces it.
 // ------------------------------------------------------------------------------------------------
 constexpr int kSpMinLevel = 6;
-constexpr int kSpMaxLevels = 12;
+constexpr int kSpMaxLevels = 32;
 
 template <typename T>
 static bool sp_upload(m3s_gn_plan* p, const T** dst, const std::vector<T>& src) {

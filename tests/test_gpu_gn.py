@@ -432,3 +432,42 @@ def test_sparse_front_iterations_and_stop(K, synth, monkeypatch, num_kf, loops):
         assert upd_err(out["sparse"][k], out["tiles"][k], g["Twc"]) <= 1e-6
     assert np.array_equal(out["sparse"][2], g["Twc"].astype(np.float32)) and np.array_equal(out["tiles"][2], out["sparse"][2])
     assert out["sparse"][3] == out["tiles"][3]
+
+
+def test_sparse_front_long_trajectory(K, synth, monkeypatch, precision):
+    """500 keyframes / 30 loop closures: the dense system (np = 3520, 55 tile rows) does not fit the co-resident
+    tile grid and would take the launch-per-step path; the sparse front leaves a tail that does.  Same dx as the
+    launch-per-step factorisation of the whole system."""
+    import ctypes as C
+    import torch
+    from mast3r_slam_b200 import _lib
+    if precision != "f64":
+        pytest.skip("the solve is independent of the accumulate precision")
+    g = synth.make_graph(31, 500, 30, 24, 32, num_pts=256)
+    dev = torch.device("cuda", 0)
+    t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a)).to(dev, dt)  # noqa: E731
+    Twc, Xs, Cs = t(g["Twc"], torch.float32), t(g["Xs"], torch.float32), t(g["Cs"], torch.float32)
+    idx, valid, Q = t(g["idx"], torch.int32), t(g["valid"].astype(np.uint8), torch.uint8), t(g["Q"], torch.float32)
+    params = K.make_params(_lib.GN_POINTS, 1, 1, 0.0, 0.0, 1.5, 0.01)
+    lib = _lib.load()
+    p = lambda x: C.c_void_p(x.data_ptr())  # noqa: E731
+    res = {}
+    for chol in ("steps", None):
+        if chol:
+            monkeypatch.setenv("M3S_GN_CHOL", chol)
+        else:
+            monkeypatch.delenv("M3S_GN_CHOL", raising=False)
+        plan = K.GNPlan(g["ii"], g["jj"], 500, 256, 1, dev)
+        _lib.check(lib.m3s_gn_set_poses(plan.handle, p(Twc), None))
+        _lib.check(lib.m3s_gn_accumulate(plan.handle, C.byref(params), p(Xs), p(Cs), p(idx), p(valid), p(Q),
+                                         0, plan.E, None))
+        _lib.check(lib.m3s_gn_solve_update(plan.handle, C.byref(params), None))
+        torch.cuda.synchronize()
+        st = plan.status()
+        assert st["applied"] == 1 and not st["failed"], (chol, st)
+        res[chol] = (plan.factor_path(), plan.sparse_info(), plan.dx().cpu().numpy().copy())
+        del plan
+    assert res["steps"][0] == 0 and res[None][0] == 3, (res["steps"][:2], res[None][:2])
+    assert res[None][1]["tail"] < 150
+    scale = np.abs(res["steps"][2]).max()
+    assert np.abs(res[None][2] - res["steps"][2]).max() <= 1e-8 * scale
