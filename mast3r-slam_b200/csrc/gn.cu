@@ -1278,10 +1278,13 @@ __global__ void __launch_bounds__(64)
 gn_assemble_kernel(const Status* __restrict__ status, const BlockRef* __restrict__ blocks,
                    const int* __restrict__ list_edge, const int* __restrict__ list_sign,
                    const double* __restrict__ edge_blocks, double* __restrict__ Hm, int np, int dim,
-                   double* __restrict__ g_out) {
+                   double* __restrict__ g_out, int* __restrict__ bs_flags, int n_bs_flags) {
     if (status->stopped | status->failed) return;
     const BlockRef br = blocks[blockIdx.x];
     const int tid = threadIdx.x;
+    // publication flags of the back-substitution: zeroed here instead of by a memset node of their own (the
+    // previous solve's kernels are complete in stream order)
+    if (blockIdx.x == 0) for (int i = tid; i < n_bs_flags; i += 64) bs_flags[i] = 0;
     if (tid < 49) {
         const int r = tid / 7, c = tid % 7;
         const int k = (r <= c) ? tri_index(r, c) : tri_index(c, r);
@@ -3194,8 +3197,10 @@ struct SpTailDev {
 
 __global__ void __launch_bounds__(64)
 sp_tail_kernel(const Status* __restrict__ status, SpDev sp, SpTailDev tl, const double* __restrict__ Hm, int np,
-               double* __restrict__ Hr, int npR) {
+               double* __restrict__ Hr, int npR, unsigned* __restrict__ tctl, int n_tctl) {
     if (status->stopped | status->failed) return;
+    // flag words of the dataflow factorisation that follows (instead of a memset node between the two)
+    if (blockIdx.x == 0) for (int i = threadIdx.x; i < n_tctl; i += 64) tctl[i] = 0u;
     const int2 rb = tl.blk[blockIdx.x];
     const int a = tl.rnode[rb.x], b = tl.rnode[rb.y];
     const int t = threadIdx.x;
@@ -4007,10 +4012,10 @@ M3S_API int m3s_gn_assemble(m3s_gn_plan* plan, m3s_stream_t stream) {
         M3S_CUDA(cudaMemsetAsync(plan->Hm, 0, sizeof(double) * (size_t)(plan->np + 1) * plan->np, st));
         plan->hm_clean = true;
     }
-    M3S_CUDA(cudaMemsetAsync(plan->flags, 0, sizeof(int) * std::max(plan->np / kNB, 1), st));
     gn_assemble_kernel<<<plan->nblocks_H, 64, 0, st>>>(plan->status, plan->blocks, plan->list_edge,
                                                        plan->list_sign, plan->edge_blocks, plan->Hm,
-                                                       plan->np, plan->dim, plan->g);
+                                                       plan->np, plan->dim, plan->g, plan->flags,
+                                                       std::max(plan->np / kNB, 1));
     if (int rc = launch_ok("gn_assemble_kernel")) return rc;
     if (plan->np > plan->dim && !plan->sp_on) {   // (the sparse front reads keyframe blocks only)
         gn_pad_diag_kernel<<<1, 32, 0, st>>>(plan->status, plan->Hm, plan->np, plan->dim);
@@ -4130,11 +4135,10 @@ static int enqueue_sparse_front(m3s_gn_plan* plan, cudaStream_t st, bool capturi
         sp_level_kernel<<<n, kSpThreads, kSpLevelSmem, st>>>(plan->status, plan->sp, b, plan->Hm, np);
         if (int rc = launch_ok("sp_level_kernel")) return rc;
     }
-    sp_tail_kernel<<<plan->sp_ntail_blocks, 64, 0, st>>>(plan->status, plan->sp, plan->spt, plan->Hm, np,
-                                                         plan->sp_Hr, npR);
-    if (int rc = launch_ok("sp_tail_kernel")) return rc;
     const int nt = (npR + kTS - 1) / kTS, grid = plan->sp_tiles_grid;
-    M3S_CUDA(cudaMemsetAsync(plan->tctl, 0, sizeof(unsigned) * tl_ctl_words(nt), st));
+    sp_tail_kernel<<<plan->sp_ntail_blocks, 64, 0, st>>>(plan->status, plan->sp, plan->spt, plan->Hm, np,
+                                                         plan->sp_Hr, npR, plan->tctl, tl_ctl_words(nt));
+    if (int rc = launch_ok("sp_tail_kernel")) return rc;
     int first_diag = std::max(0, std::min(sm_count_current(), grid) - nt);
     void* args[] = {&plan->status, &plan->sp_Hr, &plan->Lm, &plan->Linv, const_cast<int*>(&npR),
                     &plan->tctl, &first_diag, &plan->timeline};

@@ -9,7 +9,7 @@ TAG=${1:-r1}
 OUT=gpurun_out
 mkdir -p $OUT
 CMD="python bench.py --pairs 8 --steps 1 --warmup 3 --no-cpu --no-e2e --gn-iters 1"
-KREGEX='regex:iter_proj|refine_|gn_|chol_|prep_kernel|match_tail'
+KREGEX='regex:iter_proj|refine_|gn_|chol_|sp_|prep_|match_tail'
 $CMD > $OUT/plain_$TAG.log 2>&1 || { echo "plain run failed"; tail -20 $OUT/plain_$TAG.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KREGEX" -c 1500 --csv \
     --log-file $OUT/launches_$TAG.csv $CMD > $OUT/ncu_list_$TAG.log 2>&1
