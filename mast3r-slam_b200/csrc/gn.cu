@@ -3709,8 +3709,33 @@ M3S_API m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii, const int32_t* jj, in
 #endif
         const long long min_ch = std::max<long long>(1, (N + M3S_ACC_MAX_CHUNK - 1) / M3S_ACC_MAX_CHUNK);
         nch = std::min(std::max(nch, min_ch), max_ch);
+#ifndef M3S_ACC_NO_WAVE_FIT
+        // Wave fit: (edge, chunk) CTAs of equal length run in waves of 3 per SM (the streamed kernel's residency),
+        // so the pass costs ceil(CTAs / slots) chunk times: among the chunk counts near the target take the one
+        // with the cheapest last wave (~400 points of fixed cost per CTA, from the 16 k / 32 k / 64 k A/B).
+        // Only for passes of a few waves, where the last one matters -- config 3 (40 edges): 23 chunks = 2.07 ->
+        // 3 waves, the fit takes one full wave: 0.128 -> 0.107 ms per iteration; config 5 (13.5 waves) measured no
+        // gain from 7 x 28 160 instead of 6 x 32 768 (1.152 vs 1.149 ms) and keeps its chunking.  Depends on the
+        // plan only (all edges, N, SM count), so every rank of a sharded solve chunks -- and rounds -- identically.
+        if (n_active > 0 && n_active * nch <= 4 * 3LL * sms) {
+            const long long slots = 3LL * sms;
+            const long long hi = std::min(max_ch, std::max(nch + 6, min_ch + 6));
+            long long best_cost = -1, best = nch;
+            for (long long c = std::max<long long>(std::min(nch, min_ch), 1); c <= hi; ++c) {
+                if (c < min_ch) continue;
+                long long cpc = (N + c - 1) / c;
+                cpc = std::max<long long>(((cpc + 511) / 512) * 512, 512);   // whole stages of the streamed kernel
+                const long long real = std::max<long long>(1, (N + cpc - 1) / cpc);
+                const long long waves = (n_active * real + slots - 1) / slots;
+                const long long cost = waves * (cpc + 400);
+                if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = c; }
+            }
+            nch = best;
+        }
+#endif
         long long cp = (N + nch - 1) / std::max<long long>(nch, 1);
         cp = std::max<long long>(((cp + kAccThreads - 1) / kAccThreads) * kAccThreads, kAccThreads);
+        if (N >= 4096) cp = ((cp + 511) / 512) * 512;   // whole 512-point stages (streamed kernel)
         p->chunk_pts = cp;
         p->nchunks = (int)std::max<long long>(1, (N + cp - 1) / cp);
     }
@@ -3875,7 +3900,7 @@ M3S_API int m3s_gn_accumulate(m3s_gn_plan* plan, const m3s_gn_params* gp, const 
             const uintptr_t al_all = al | reinterpret_cast<uintptr_t>(valid);
             int impl = acc_impl();
             const bool stream_ok = ((plan->N & 15) == 0) && ((al_all & 15) == 0) &&
-                                   plan->N < (1LL << 29) && (plan->chunk_pts % 1024) == 0;
+                                   plan->N < (1LL << 29) && (plan->chunk_pts % 512) == 0;   // whole 512-point stages
             if (!stream_ok) impl = 0;
 #define M3S_ACCS(MODE, TPB, ST, MINB, SLIM)                                                          \
     do {                                                                                         \
