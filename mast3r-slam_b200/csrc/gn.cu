@@ -3713,21 +3713,25 @@ M3S_API m3s_gn_plan* m3s_gn_plan_create(const int32_t* ii, const int32_t* jj, in
         // Wave fit: (edge, chunk) CTAs of equal length run in waves of 3 per SM (the streamed kernel's residency),
         // so the pass costs ceil(CTAs / slots) chunk times: among the chunk counts near the target take the one
         // with the cheapest last wave (~400 points of fixed cost per CTA, from the 16 k / 32 k / 64 k A/B).
-        // Only for passes of a few waves, where the last one matters -- config 3 (40 edges): 23 chunks = 2.07 ->
-        // 3 waves, the fit takes one full wave: 0.128 -> 0.107 ms per iteration; config 5 (13.5 waves) measured no
-        // gain from 7 x 28 160 instead of 6 x 32 768 (1.152 vs 1.149 ms) and keeps its chunking.  Depends on the
-        // plan only (all edges, N, SM count), so every rank of a sharded solve chunks -- and rounds -- identically.
-        if (n_active > 0 && n_active * nch <= 4 * 3LL * sms) {
+        // The plan does not know how many ranks will share its edges (and must chunk identically on all of them:
+        // the chunk sums are part of the bitwise result), so the fit is over 1 / 2 / 4 / 8 equal shares at once.
+        // Config 5 (1000 edges): 6 x 32 768 = 13.5 / 6.8 / 3.4 / 1.7 waves -> 7 x 28 160 = 15.8 / 7.9 / 3.9 / 1.97
+        // (measured: 1 GPU 1.149 -> 1.152 ms, i.e. nothing; 8 GPUs see the A/B in DESIGN.md); config 3 (40 edges):
+        // 23 chunks = 2.07 waves -> one full wave, 0.128 -> 0.107 ms per iteration.
+        if (n_active > 0) {
             const long long slots = 3LL * sms;
             const long long hi = std::min(max_ch, std::max(nch + 6, min_ch + 6));
             long long best_cost = -1, best = nch;
-            for (long long c = std::max<long long>(std::min(nch, min_ch), 1); c <= hi; ++c) {
-                if (c < min_ch) continue;
+            for (long long c = min_ch; c <= hi; ++c) {
                 long long cpc = (N + c - 1) / c;
                 cpc = std::max<long long>(((cpc + 511) / 512) * 512, 512);   // whole stages of the streamed kernel
                 const long long real = std::max<long long>(1, (N + cpc - 1) / cpc);
-                const long long waves = (n_active * real + slots - 1) / slots;
-                const long long cost = waves * (cpc + 400);
+                long long cost = 0;
+                for (int w = 1; w <= 8; w *= 2) {
+                    const long long share = (n_active + w - 1) / w;
+                    if (w > 1 && share * real < slots) break;   // a share below one wave: not a sharding worth fitting
+                    cost += w * ((share * real + slots - 1) / slots) * (cpc + 400);
+                }
                 if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = c; }
             }
             nch = best;
