@@ -3219,7 +3219,7 @@ sp_tail_kernel(const Status* __restrict__ status, SpDev sp, SpTailDev tl, const 
 }
 
 // The whole back end of the sparse-front solve in ONE CTA: tail x into natural order, the levels in reverse
-// (x_j = G^-T (y_j - sum_a W_aj^T x_a); 16 keyframes at a time, 56 threads each), the ||dx|| test before applying
+// (x_j = G^-T (y_j - sum_a W_aj^T x_a); 32 keyframes at a time, one warp each), the ||dx|| test before applying
 // (gauss_newton.py:263-265) and the Sim3 retraction.  (As one launch per level + scatter + finish this was seven
 // launches of 3-10 us each for ~50k FMAs of work.)
 __global__ void __launch_bounds__(1024)
@@ -3228,46 +3228,40 @@ sp_back_finish_kernel(Status* __restrict__ status, SpDev sp, const int* __restri
                       double* __restrict__ dx, int dim, int num_free, const int* __restrict__ free_kf,
                       double delta_thresh, double* __restrict__ poses, int metal) {
     if (status->stopped | status->failed) return;
-    __shared__ double part[16][8][7];
-    __shared__ double tv[16][7];
     __shared__ double red[32];
     __shared__ int decision;  // 0 apply, 1 stop, 2 fail
-    const int tid = threadIdx.x, grp = tid >> 6, t = tid & 63;
+    const int tid = threadIdx.x;
     for (int i = tid; i < 7 * nR; i += 1024) dx[7 * rnode[i / 7] + i % 7] = __ldcg(xsol + i);
     __syncthreads();
+    // one WARP per keyframe (32 at a time), everything inside the warp: lane = 7 p + k holds partial p (rows
+    // 1 + p, 5 + p, ...) of component k; the CTA only synchronises between levels
+    const int warp = tid >> 5, lane = tid & 31;
     for (int l = levels - 1; l >= 0; --l) {
         const int b = level_begin[l], n = level_begin[l + 1] - b;
-        for (int it = 0; it < n; it += 16) {
-            const int e = b + it + grp;
-            const bool on = it + grp < n;
-            int r0 = 0, nrows = 0;
-            if (on) { r0 = sp.row_ptr[e]; nrows = sp.row_ptr[e + 1] - r0; }
-            if (on && t < 56) {
-                const int k = t % 7, p = t / 7;   // partial p of component k: rows s = 1 + p, 9 + p, ...
-                double acc = 0.0;
-                for (int s = 1 + p; s < nrows; s += 8) {
+        for (int it = warp; it < n; it += 32) {
+            const int e = b + it;
+            const int r0 = sp.row_ptr[e], nrows = sp.row_ptr[e + 1] - r0;
+            const int k = lane % 7, p = lane / 7;            // lanes 28 .. 31: p = 4, idle
+            double acc = 0.0;
+            if (lane < 28) {
+                for (int s = 1 + p; s < nrows; s += 4) {
                     const double* w = sp.W + (size_t)(r0 + s) * 49 + k;
                     const double* xa = dx + 7 * sp.row_node[r0 + s];
 #pragma unroll
                     for (int r = 0; r < 7; ++r) acc = fma(w[r * 7], xa[r], acc);
                 }
-                part[grp][p][k] = acc;
             }
-            __syncthreads();
-            if (on && t < 7) {
-                double v = sp.y[(size_t)e * 7 + t];
+            acc += __shfl_down_sync(0xffffffffu, acc, 14);   // partials 2, 3 onto 0, 1
+            acc += __shfl_down_sync(0xffffffffu, acc, 7);    // partial 1 onto 0: lanes 0 .. 6 hold the sums
+            const double tk = (lane < 7) ? sp.y[(size_t)e * 7 + lane] - acc : 0.0;
+            const double* gi = sp.Ginv + (size_t)e * 49;
+            double d = 0.0;
 #pragma unroll
-                for (int p = 0; p < 8; ++p) v -= part[grp][p][t];
-                tv[grp][t] = v;
+            for (int kk = 0; kk < 7; ++kk) {
+                const double t_kk = __shfl_sync(0xffffffffu, tk, kk);
+                if (lane < 7) d = fma(gi[kk * 7 + lane], t_kk, d);
             }
-            __syncthreads();
-            if (on && t < 7) {
-                const double* gi = sp.Ginv + (size_t)e * 49;
-                double d = 0.0;
-#pragma unroll
-                for (int k = 0; k < 7; ++k) d = fma(gi[k * 7 + t], tv[grp][k], d);
-                dx[7 * sp.enode[e] + t] = d;
-            }
+            if (lane < 7) dx[7 * sp.enode[e] + lane] = d;
         }
         __syncthreads();   // the level's x is visible to the whole CTA before the next level reads it
     }
